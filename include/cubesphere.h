@@ -1,0 +1,234 @@
+/*
+ * cubesphere.h -- C ABI of the B200-native cubed-sphere shallow-water hot path.
+ *
+ * One explicit time step over the six gnomonic-equiangular panels: halo fill,
+ * finite-volume flux/tendency stencil, fused Runge-Kutta stage update, and the
+ * mass / energy reductions, as hand-written sm_100a CUDA kernels.
+ *
+ * Boundary rules
+ *   - plain C: pointers, sizes, PODs; no C++ or torch types cross this header;
+ *   - every device pointer is caller-owned memory on the context's device;
+ *   - every call only ENQUEUES work on the given stream (a cudaStream_t passed as
+ *     void*; NULL = the legacy default stream) and never synchronises, except
+ *     cs_ctx_create / cs_ctx_destroy / cs_step_host which own their synchronisation;
+ *   - return value 0 = success, negative = CS_E_* below; the text of the last
+ *     error of a context (or of the calling thread when ctx is NULL) is
+ *     cs_last_error();
+ *   - there is no CPU fallback: without a CUDA device every compute entry point
+ *     fails with CS_E_CUDA.
+ *
+ * State layout (reference JAX-DevLab-Examples.py:141,174; deck slide 11):
+ *   each field is one dense array  [tile_count][n + 2g][n + 2g], x fastest,
+ *   n = N / tiles_per_edge, interior cells at [g, g + n) on both axes, tile id =
+ *   face * p^2 + ty * p + tx.  A context owns the contiguous tile range
+ *   [tile_begin, tile_begin + tile_count) -- the block partition of axis 0 that
+ *   the reference gets from NamedSharding(mesh, P('tiles'))
+ *   (JAX-DevLab-Examples.py:77-79).  h is the fluid depth (m); u, v are the
+ *   panel-local contravariant velocity components (rad/s).
+ *
+ * "Replaces" below cites the reference interface each entry point stands in for
+ * (file /root/reference/JAX-DevLab-Examples.py, abbreviated PY; deck = the PDF).
+ */
+#ifndef CUBESPHERE_H_
+#define CUBESPHERE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CS_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define CS_API __attribute__((visibility("default")))
+#else
+#define CS_API
+#endif
+
+/* error codes */
+#define CS_OK 0
+#define CS_E_INVALID (-1)        /* bad argument / configuration (Python: ValueError)        */
+#define CS_E_UNSUPPORTED (-2)    /* valid but not implemented (Python: NotImplementedError)  */
+#define CS_E_CUDA (-3)           /* a CUDA runtime call failed; see cs_last_error            */
+#define CS_E_NOMEM (-4)          /* device or host allocation failed                         */
+
+/* enums */
+#define CS_F32 0
+#define CS_F64 1
+#define CS_RK_EULER 1
+#define CS_RK_SSPRK2 2
+#define CS_RK_SSPRK3 3
+#define CS_LIM_NONE 0
+#define CS_LIM_MINMOD 1
+#define CS_LIM_MC 2
+#define CS_KERNEL_AUTO 0         /* fastest validated stage kernel                           */
+#define CS_KERNEL_NAIVE 1        /* one thread per cell, global loads only (cross-check)     */
+#define CS_KERNEL_MARCH 2        /* register-marching kernel, direct global loads            */
+#define CS_KERNEL_TMA 3          /* register-marching kernel fed by a TMA shared-memory ring */
+
+typedef struct cs_ctx cs_ctx;
+
+/* Versioned POD.  Zero-initialise, fill, pass to cs_ctx_create. */
+typedef struct cs_config {
+    int32_t abi_version;      /* CS_ABI_VERSION                                              */
+    int32_t N;                /* cells per face edge (C48 -> 48)                             */
+    int32_t tiles_per_edge;   /* p; 6 p^2 tiles (PY:40).  reference supports 1 only (PY:31)  */
+    int32_t halo;             /* g; the step needs g >= 2, plain halo fills accept g >= 1    */
+    int32_t dtype;            /* CS_F32 | CS_F64                                             */
+    int32_t rk;               /* CS_RK_*                                                     */
+    int32_t limiter;          /* CS_LIM_*                                                    */
+    int32_t advect_only;      /* 1: velocity frozen (Williamson case 1)                      */
+    int32_t device;           /* CUDA device ordinal                                         */
+    int32_t tile_begin;       /* first tile owned by this context                            */
+    int32_t tile_count;       /* number of tiles owned; 0 = all 6 p^2                        */
+    int32_t kernel;           /* CS_KERNEL_*                                                 */
+    int32_t fused_halo;       /* 1: stage kernel stores boundary cells into neighbour ghosts */
+    int32_t reserved[3];
+    double radius;            /* a      (0 -> 6.37122e6 m)                                   */
+    double omega;             /* Omega  (0 -> 7.292e-5 1/s; set advect_only for no rotation) */
+    double gravity;           /* g      (0 -> 9.80616 m/s^2)                                 */
+    double axis[3];           /* unit rotation axis (all 0 -> (0,0,1))                       */
+    const double* tangents;   /* optional host table of N centre tangents tan(alpha_i);      */
+                              /* NULL -> computed internally                                 */
+} cs_config;
+
+/* Library version of this ABI.  Replaces: nothing (the reference has no FFI). */
+CS_API int cs_abi_version(void);
+
+/* Text of the last error of ctx, or of the calling thread when ctx == NULL. */
+CS_API const char* cs_last_error(const cs_ctx* ctx);
+
+/*
+ * Validate the configuration, select the device, build the seam gather tables
+ * and metric tables, allocate the Runge-Kutta scratch state.
+ * Replaces: setup_sharding's validation of tiles_per_edge / divisibility
+ * (PY:31-57), create_communication_schedule (PY:105-139) and the factory
+ * make_halo_exchange(schedule, N) (PY:199-246), whose frozen static arguments
+ * (faces, edges, ops, N) become the context's tables.
+ */
+CS_API int cs_ctx_create(const cs_config* cfg, cs_ctx** out);
+CS_API int cs_ctx_destroy(cs_ctx* ctx);
+
+/*
+ * Fill every ghost cell (4 edge strips of width g and 4 g x g corner blocks per
+ * tile) of one scalar field in place.  Bit-exact copy of neighbour interiors
+ * with the seam's index reversal.
+ * Replaces: cubesphere_halo_exchange(field_ghosts) (PY:238-242) = 12 x
+ * exchange_edge_pair (PY:166-197) incl. extract_boundary_data / apply_operations
+ * / set_ghost_data (PY:143-163,184-195); ghost corners, which the reference never
+ * writes, get the rule of DESIGN.md section 2.4.
+ * Requires tile_count == 6 p^2 (single-device context); see cs_halo_pack for shards.
+ */
+CS_API int cs_halo_fill_scalar(cs_ctx* ctx, void* field, void* stream);
+
+/*
+ * Same for a panel-local vector field: copy + index reversal + the seam's signed
+ * permutation of the two components (bit-exact).
+ * Replaces: the reference's "Cartesian Velocity Exchange" (deck slide 18), which
+ * side-steps the rotation by exchanging three Cartesian scalars.
+ */
+CS_API int cs_halo_fill_vector(cs_ctx* ctx, void* u, void* v, void* stream);
+
+/* h, u, v in one launch.  Replaces: three calls of the above per RK stage. */
+CS_API int cs_halo_fill_state(cs_ctx* ctx, void* h, void* u, void* v, void* stream);
+
+/*
+ * Optional position-dependent 2x2 rotation of vector ghosts: rot is a HOST array
+ * [ghost cells][4] (row-major 2x2, fp64) in the order of cs_halo_table_info;
+ * ghost (u, v) = R (u, v)_neighbour, evaluated as two products and one sum per
+ * component without FMA contraction, so a CPU evaluation in the same order is
+ * bit-identical.  NULL restores the signed permutation.
+ */
+CS_API int cs_halo_set_rotation(cs_ctx* ctx, const double* rot, size_t n_ghost);
+
+/*
+ * Ghost-cell table of the context, for callers that want to build rotation
+ * tables: writes up to cap entries of (dst_offset, src_offset, code) and returns
+ * the ghost-cell count in *n_ghost.  Offsets are element offsets into a field of
+ * the local shard; src_offset is -1 for cells whose source lives on another
+ * context.  Any output pointer may be NULL.
+ */
+CS_API int cs_halo_table_info(const cs_ctx* ctx, size_t cap, int64_t* dst_offset, int64_t* src_offset,
+                       int32_t* code, size_t* n_ghost);
+
+/*
+ * Static bottom topography hs (same layout and dtype as the state); interior
+ * cells are copied into the context and its ghosts filled.  NULL clears it.
+ */
+CS_API int cs_set_topography(cs_ctx* ctx, const void* hs, void* stream);
+
+/*
+ * One fused Runge-Kutta stage on all owned tiles:
+ *     qout = a * q0 + b * (qs + dt * L(qs))      on interior cells,
+ * L = PLR-upwind continuity + vector-invariant momentum with Coriolis and
+ * pressure-gradient sources.  qs must be halo-filled; qout's ghosts are filled
+ * on return (fused push or a halo launch).  qout may alias q0, never qs.
+ * When a == 0, q0 is not read.  diag_out (device double[2], may be NULL) receives
+ * mass and total energy of qout.
+ * Replaces: the "Numerics (FV)" box driven by jax.shard_map (deck slides 6-7);
+ * not shipped in the reference.
+ */
+CS_API int cs_rk_stage(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3],
+                double a, double b, double dt, double* diag_out, void* stream);
+
+/*
+ * One explicit time step, in place: h, u, v must be halo-filled on entry and are
+ * halo-filled on return.  Replaces: step(state, dt) of BASELINE.json's
+ * north_star (the solver driver behind deck slide 7; not shipped).
+ * diag_out as in cs_rk_stage (values of the new state), may be NULL.
+ */
+CS_API int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out, void* stream);
+
+/*
+ * Mass  M = sum sqrt(G) h dalpha dbeta  and total energy
+ * E = sum sqrt(G) (h K + g h^2 / 2 + g h hs) dalpha dbeta  over the owned interior
+ * cells, accumulated in fp64 in a fixed order (deterministic); out = device
+ * double[2].  Replaces: conservation diagnostics named by north_star; not shipped.
+ */
+CS_API int cs_diagnostics(cs_ctx* ctx, const void* h, const void* u, const void* v, double* out, void* stream);
+
+/*
+ * Host-buffer convenience entry (what a ctypes / cgo style caller with NumPy
+ * arrays uses): copies h, u, v (host, full padded layout) to the device, fills
+ * halos, runs nsteps steps, writes mass/energy of the final state to diag_host[2]
+ * (may be NULL) and, when copy_back != 0, copies the state back.  Synchronises.
+ */
+CS_API int cs_step_host(cs_ctx* ctx, void* h_host, void* u_host, void* v_host, double dt, int nsteps,
+                 double* diag_host, int copy_back);
+
+/*
+ * Sharded halo exchange (tile_count < 6 p^2).  The context splits its ghost
+ * cells into local ones (filled by cs_halo_fill_* / the stage kernel) and remote
+ * ones.  For each peer context r (in order of tile_begin) cs_halo_plan reports
+ * how many cells this context sends to and receives from r; cs_halo_pack gathers
+ * the boundary cells of h, u, v that peers need into sendbuf (3 values per cell,
+ * peers in rank order), the caller moves the bytes (NCCL send/recv, all_to_all or
+ * peer copies), and cs_halo_unpack scatters recvbuf into the ghosts applying the
+ * seam permutation.  nfields = 1 packs a single scalar field (h only).
+ * Replaces: the cross-device copies GSPMD inserts for .at[face].set(...) on an
+ * array sharded with P('tiles') (PY:79,192-195).
+ */
+CS_API int cs_halo_plan(cs_ctx* ctx, int n_peers, const int32_t* peer_tile_begin,
+                 const int32_t* peer_tile_count, int64_t* send_counts, int64_t* recv_counts);
+CS_API int cs_halo_pack(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields,
+                 void* sendbuf, void* stream);
+CS_API int cs_halo_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u, void* v, int nfields,
+                   void* stream);
+
+/*
+ * Split stage for overlap on shards: part = 0 computes cells that need no remote
+ * ghost, part = 1 the rim that does, part = 2 everything.  Same contract as
+ * cs_rk_stage otherwise (no halo fill of qout is done for parts 0 / 1).
+ */
+CS_API int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3],
+                     double a, double b, double dt, int part, void* stream);
+
+/* Number of kernels this library has launched on ctx since creation (bench bookkeeping). */
+CS_API int64_t cs_launch_count(const cs_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUBESPHERE_H_ */

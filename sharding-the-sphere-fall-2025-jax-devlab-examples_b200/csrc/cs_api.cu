@@ -1,0 +1,137 @@
+// Entry points that compose the kernels: topography, one RK stage, one step, host-buffer step.
+#include "cs_internal.cuh"
+
+namespace {
+
+struct RkPair { double a, b; };
+
+// Shu-Osher pairs; a is 1 - b so that a + b == 1 exactly in binary floating point
+// (1/3 + 2/3 rounds to 1 - 2^-54 and would leak mass every step).
+int rk_pairs(int rk, RkPair out[3]) {
+    out[0] = {0.0, 1.0};
+    if (rk == CS_RK_EULER) return 1;
+    if (rk == CS_RK_SSPRK2) {
+        out[1] = {0.5, 0.5};
+        return 2;
+    }
+    out[1] = {0.75, 0.25};
+    out[2] = {1.0 - 2.0 / 3.0, 2.0 / 3.0};
+    return 3;
+}
+
+int check_step_ready(cs_ctx* ctx, const char* who) {
+    if (ctx->g < 2) return cs_fail(ctx, CS_E_INVALID, "%s: the stencil needs halo >= 2, the context has %d", who, ctx->g);
+    return CS_OK;
+}
+
+bool single_device(const cs_ctx* ctx) { return ctx->T == ctx->T_all; }
+
+}  // namespace
+
+extern "C" int cs_set_topography(cs_ctx* ctx, const void* hs, void* stream) {
+    if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_set_topography: NULL context");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!hs) {
+        ctx->has_topo = false;
+        return CS_OK;
+    }
+    CS_CUDA(ctx, cudaMemcpyAsync(ctx->topo, hs, ctx->field_elems * ctx->esize, cudaMemcpyDeviceToDevice, s));
+    ctx->has_topo = true;
+    // local ghosts now; remote ghosts (shards) are the caller's job via cs_halo_pack(nfields = 1)
+    return cs_launch_halo(ctx, ctx->topo, nullptr, nullptr, 1, s);
+}
+
+extern "C" int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a,
+                                double b, double dt, int part, void* stream) {
+    if (!ctx || !q0 || !qs || !qout) return cs_fail(ctx, CS_E_INVALID, "cs_rk_stage: NULL argument");
+    int rc = check_step_ready(ctx, "cs_rk_stage");
+    if (rc) return rc;
+    if (part < 0 || part > 2) return cs_fail(ctx, CS_E_INVALID, "cs_rk_stage_part: part = %d must be 0, 1 or 2", part);
+    for (int k = 0; k < 3; ++k) {
+        if (!qs[k] || !qout[k] || (a != 0.0 && !q0[k])) return cs_fail(ctx, CS_E_INVALID, "cs_rk_stage: NULL field pointer");
+        for (int l = 0; l < 3; ++l)
+            if (qout[k] == qs[l]) return cs_fail(ctx, CS_E_INVALID, "cs_rk_stage: qout must not alias qs (stencil input)");
+    }
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return cs_launch_stage(ctx, q0, qs, qout, a, b, dt, part, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int cs_rk_stage(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a,
+                           double b, double dt, double* diag_out, void* stream) {
+    int rc = cs_rk_stage_part(ctx, q0, qs, qout, a, b, dt, 2, stream);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if ((rc = cs_launch_halo(ctx, qout[0], qout[1], qout[2], 3, s))) return rc;
+    if (diag_out) return cs_launch_diag(ctx, qout[0], qout[1], qout[2], diag_out, s);
+    return CS_OK;
+}
+
+extern "C" int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out, void* stream) {
+    if (!ctx || !h || !u || !v) return cs_fail(ctx, CS_E_INVALID, "cs_step: NULL argument");
+    int rc = check_step_ready(ctx, "cs_step");
+    if (rc) return rc;
+    if (!single_device(ctx))
+        return cs_fail(ctx, CS_E_INVALID,
+                       "cs_step: the context owns %d of %d tiles; drive shards with cs_rk_stage_part + cs_halo_pack/unpack",
+                       ctx->T, ctx->T_all);
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    RkPair pr[3];
+    const int ns = rk_pairs(ctx->cfg.rk, pr);
+    void* q0[3] = {h, u, v};
+    const void* cur[3] = {h, u, v};
+    for (int k = 0; k < ns; ++k) {
+        // the last stage writes the caller's arrays in place (it reads them point-wise only);
+        // a single-stage scheme has nothing else to read from, so it goes through scratch
+        void** dst = (k == ns - 1 && ns > 1) ? q0 : (k % 2 == 0 ? ctx->qa : ctx->qb);
+        if ((rc = cs_launch_stage(ctx, q0, cur, dst, pr[k].a, pr[k].b, dt, 2, nullptr, s))) return rc;
+        if ((rc = cs_launch_halo(ctx, dst[0], dst[1], dst[2], 3, s))) return rc;
+        for (int c = 0; c < 3; ++c) cur[c] = dst[c];
+    }
+    if (ns == 1)
+        for (int c = 0; c < 3; ++c)
+            CS_CUDA(ctx, cudaMemcpyAsync(q0[c], ctx->qa[c], ctx->field_elems * ctx->esize, cudaMemcpyDeviceToDevice, s));
+    if (diag_out) return cs_launch_diag(ctx, h, u, v, diag_out, s);
+    return CS_OK;
+}
+
+extern "C" int cs_step_host(cs_ctx* ctx, void* h_host, void* u_host, void* v_host, double dt, int nsteps, double* diag_host,
+                            int copy_back) {
+    if (!ctx || !h_host || !u_host || !v_host) return cs_fail(ctx, CS_E_INVALID, "cs_step_host: NULL argument");
+    if (nsteps < 0) return cs_fail(ctx, CS_E_INVALID, "cs_step_host: nsteps = %d must be >= 0", nsteps);
+    int rc = check_step_ready(ctx, "cs_step_host");
+    if (rc) return rc;
+    if (!single_device(ctx)) return cs_fail(ctx, CS_E_INVALID, "cs_step_host needs a context that owns all tiles");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t bytes = ctx->field_elems * ctx->esize;
+    // device copy of the caller's host state, allocated on first use and kept by the context
+    void** d = ctx->host_state;
+    for (int k = 0; k < 3; ++k)
+        if (!d[k] && cudaMalloc(&d[k], bytes) != cudaSuccess)
+            return cs_fail(ctx, CS_E_NOMEM, "cs_step_host: cudaMalloc of %zu bytes failed", bytes);
+    cudaStream_t s = 0;
+    void* hostp[3] = {h_host, u_host, v_host};
+    auto cleanup = [&](int code) {
+        cudaStreamSynchronize(s);
+        return code;
+    };
+    for (int k = 0; k < 3; ++k)
+        if (cudaMemcpyAsync(d[k], hostp[k], bytes, cudaMemcpyHostToDevice, s) != cudaSuccess)
+            return cleanup(cs_fail(ctx, CS_E_CUDA, "cs_step_host: host-to-device copy failed"));
+    if ((rc = cs_launch_halo(ctx, d[0], d[1], d[2], 3, s))) return cleanup(rc);
+    for (int it = 0; it < nsteps; ++it)
+        if ((rc = cs_step(ctx, d[0], d[1], d[2], dt, nullptr, s))) return cleanup(rc);
+    if (diag_host) {
+        if ((rc = cs_launch_diag(ctx, d[0], d[1], d[2], ctx->d_diag, s))) return cleanup(rc);
+        if (cudaMemcpyAsync(diag_host, ctx->d_diag, 2 * sizeof(double), cudaMemcpyDeviceToHost, s) != cudaSuccess)
+            return cleanup(cs_fail(ctx, CS_E_CUDA, "cs_step_host: device-to-host copy failed"));
+    }
+    if (copy_back)
+        for (int k = 0; k < 3; ++k)
+            if (cudaMemcpyAsync(hostp[k], d[k], bytes, cudaMemcpyDeviceToHost, s) != cudaSuccess)
+                return cleanup(cs_fail(ctx, CS_E_CUDA, "cs_step_host: device-to-host copy failed"));
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return cs_fail(ctx, CS_E_CUDA, "cs_step_host: %s", cudaGetErrorString(e));
+    return CS_OK;
+}

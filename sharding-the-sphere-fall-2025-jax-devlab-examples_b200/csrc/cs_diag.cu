@@ -1,0 +1,108 @@
+// K3 -- mass and total-energy reductions.
+//
+// Per-thread fp64 accumulation over a fixed grid-stride pattern, warp shuffles, one partial
+// per block, and the last block to finish adds the partials in index order: the result is
+// deterministic for a given configuration (no floating-point atomics anywhere).
+#include "cs_internal.cuh"
+#include "cs_cell.cuh"
+
+namespace {
+
+constexpr int DIAG_THREADS = 256;
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// block-level sum of two values; result valid in thread 0
+__device__ __forceinline__ void block_sum2(double& a, double& b) {
+    __shared__ double sa[DIAG_THREADS / 32], sb[DIAG_THREADS / 32];
+    a = warp_sum(a);
+    b = warp_sum(b);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) sa[w] = a, sb[w] = b;
+    __syncthreads();
+    if (w == 0) {
+        a = l < DIAG_THREADS / 32 ? sa[l] : 0.0;
+        b = l < DIAG_THREADS / 32 ? sb[l] : 0.0;
+        a = warp_sum(a);
+        b = warp_sum(b);
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(DIAG_THREADS)
+diag_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restrict__ v, const R* __restrict__ topo,
+            const double* __restrict__ xt, int n, int g, int m, int p, int T, int t0, double a2, double grav, double darea,
+            double* __restrict__ partials, unsigned int* __restrict__ ticket, double* __restrict__ out) {
+    double mass = 0.0, energy = 0.0;
+    const int64_t cells = (int64_t)T * n * n;
+    for (int64_t c = blockIdx.x * (int64_t)DIAG_THREADS + threadIdx.x; c < cells; c += (int64_t)gridDim.x * DIAG_THREADS) {
+        const int t = (int)(c / ((int64_t)n * n));
+        const int r = (int)(c - (int64_t)t * n * n);
+        const int j = r / n, i = r - j * n;
+        const TileCoord tc = cs_tile_coord(t + t0, p);
+        const size_t o = (size_t)t * m * m + (size_t)(j + g) * m + (i + g);
+        const Metric<double> M = cs_metric<double>(xt[tc.tx * n + i + g], xt[tc.ty * n + j + g], a2);
+        const double hh = (double)h[o], uu = (double)u[o], vv = (double)v[o];
+        const double hs = topo ? (double)topo[o] : 0.0;
+        const Derived<double> D = cs_derive<double>(M, hh, uu, vv, hs, grav);
+        const double w = M.sg * darea;
+        mass += w * hh;
+        energy += w * (hh * D.K + 0.5 * grav * hh * hh + grav * hh * hs);
+    }
+    block_sum2(mass, energy);
+    __shared__ bool last;
+    if (threadIdx.x == 0) {
+        partials[2 * blockIdx.x] = mass;
+        partials[2 * blockIdx.x + 1] = energy;
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last) {   // fixed-order final sum by the last block
+        __threadfence();
+        double a = 0.0, b = 0.0;
+        for (int k = threadIdx.x; k < (int)gridDim.x; k += DIAG_THREADS) {
+            a += partials[2 * k];
+            b += partials[2 * k + 1];
+        }
+        block_sum2(a, b);
+        if (threadIdx.x == 0) {
+            out[0] = a, out[1] = b;
+            *ticket = 0;   // ready for the next launch on this stream
+        }
+    }
+}
+
+}  // namespace
+
+int cs_launch_diag(cs_ctx* ctx, const void* h, const void* u, const void* v, double* out, cudaStream_t s) {
+    const int64_t cells = (int64_t)ctx->T * ctx->n * ctx->n;
+    int64_t blocks = (cells + DIAG_THREADS * 4 - 1) / (DIAG_THREADS * 4);
+    const int64_t cap = std::min<int64_t>(ctx->partial_cap, (int64_t)ctx->num_sms * 8);
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    const double a2 = ctx->radius * ctx->radius, darea = ctx->delta * ctx->delta;
+    if (ctx->dtype == CS_F64)
+        diag_kernel<double><<<(int)blocks, DIAG_THREADS, 0, s>>>((const double*)h, (const double*)u, (const double*)v,
+                                                                ctx->has_topo ? (const double*)ctx->topo : nullptr, ctx->d_xt64,
+                                                                ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, a2, ctx->gravity,
+                                                                darea, ctx->d_partials, ctx->d_ticket, out);
+    else
+        diag_kernel<float><<<(int)blocks, DIAG_THREADS, 0, s>>>((const float*)h, (const float*)u, (const float*)v,
+                                                               ctx->has_topo ? (const float*)ctx->topo : nullptr, ctx->d_xt64,
+                                                               ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, a2, ctx->gravity,
+                                                               darea, ctx->d_partials, ctx->d_ticket, out);
+    ctx->launches++;
+    CS_CUDA(ctx, cudaGetLastError());
+    return CS_OK;
+}
+
+extern "C" int cs_diagnostics(cs_ctx* ctx, const void* h, const void* u, const void* v, double* out, void* stream) {
+    if (!ctx || !h || !u || !v || !out) return cs_fail(ctx, CS_E_INVALID, "cs_diagnostics: NULL argument");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return cs_launch_diag(ctx, h, u, v, out, (cudaStream_t)stream);
+}

@@ -1,0 +1,249 @@
+// K1 -- ghost-cell fill (table driven), pack / unpack for sharded contexts.
+//
+// One thread per ghost cell: a gather from the neighbour's interior cell, the
+// seam's signed permutation of the two vector components, a scatter into the
+// ghost cell.  Replaces the 12 sequential exchange_edge_pair swaps of the
+// reference (JAX-DevLab-Examples.py:166-197, 238-242) with one launch; because
+// every ghost cell has exactly one writer and sources are interior cells only,
+// no staging and no 4-stage schedule are needed.
+#include "cs_internal.cuh"
+
+namespace {
+
+template <typename R>
+__device__ __forceinline__ void permute(R& a, R& b, int code) {
+    R x = (code & 1) ? b : a;
+    R y = (code & 1) ? a : b;
+    a = (code & 2) ? -x : x;
+    b = (code & 4) ? -y : y;
+}
+
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+
+// mask: bit0 scalar field h, bit1 vector field (u, v)
+template <typename R>
+__global__ void __launch_bounds__(256)
+halo_fill_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const int32_t* __restrict__ dst,
+                 const int32_t* __restrict__ src, const uint8_t* __restrict__ code, const R* __restrict__ rot,
+                 int64_t count, int mask) {
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < count; k += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t d = dst[k], s = src[k];
+        if (mask & 1) h[d] = h[s];
+        if (mask & 2) {
+            R a = u[s], b = v[s];
+            if (rot) {   // position-dependent 2x2: two products and one sum per component, never contracted
+                const R* r = rot + 4 * k;
+                R x = add_rn(mul_rn(r[0], a), mul_rn(r[1], b));
+                R y = add_rn(mul_rn(r[2], a), mul_rn(r[3], b));
+                a = x, b = y;
+            } else {
+                permute(a, b, code[k]);
+            }
+            u[d] = a, v[d] = b;
+        }
+    }
+}
+
+// sendbuf layout: for each peer block [field][cell]; the caller slices it per peer
+template <typename R>
+__global__ void __launch_bounds__(256)
+halo_pack_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restrict__ v,
+                 const int32_t* __restrict__ src, R* __restrict__ buf, const int64_t* __restrict__ peer_off,
+                 int n_peers, int64_t count, int nfields) {
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < count; k += (int64_t)gridDim.x * blockDim.x) {
+        int r = 0;
+        while (r + 1 < n_peers && k >= peer_off[r + 1]) ++r;
+        const int64_t cnt = peer_off[r + 1] - peer_off[r];
+        const int64_t base = peer_off[r] * nfields + (k - peer_off[r]);
+        const int32_t s = src[k];
+        buf[base] = h[s];
+        if (nfields == 3) {
+            buf[base + cnt] = u[s];
+            buf[base + 2 * cnt] = v[s];
+        }
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256)
+halo_unpack_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const int32_t* __restrict__ dst,
+                   const uint8_t* __restrict__ code, const R* __restrict__ buf, const int64_t* __restrict__ peer_off,
+                   int n_peers, int64_t count, int nfields) {
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < count; k += (int64_t)gridDim.x * blockDim.x) {
+        int r = 0;
+        while (r + 1 < n_peers && k >= peer_off[r + 1]) ++r;
+        const int64_t cnt = peer_off[r + 1] - peer_off[r];
+        const int64_t base = peer_off[r] * nfields + (k - peer_off[r]);
+        const int32_t d = dst[k];
+        h[d] = buf[base];
+        if (nfields == 3) {
+            R a = buf[base + cnt], b = buf[base + 2 * cnt];
+            permute(a, b, code[k]);
+            u[d] = a, v[d] = b;
+        }
+    }
+}
+
+int grid_for(const cs_ctx* ctx, int64_t count) {
+    int64_t blocks = (count + 255) / 256;
+    int64_t cap = (int64_t)ctx->num_sms * 8;
+    return (int)(blocks < 1 ? 1 : blocks > cap ? cap : blocks);
+}
+
+}  // namespace
+
+int cs_launch_halo(cs_ctx* ctx, void* h, void* u, void* v, int mask, cudaStream_t s) {
+    if (ctx->n_local == 0) return CS_OK;
+    if (ctx->dtype == CS_F64)
+        halo_fill_kernel<double><<<grid_for(ctx, ctx->n_local), 256, 0, s>>>((double*)h, (double*)u, (double*)v, ctx->d_halo_dst,
+                                                                            ctx->d_halo_src, ctx->d_halo_code,
+                                                                            (const double*)ctx->d_rot, ctx->n_local, mask);
+    else
+        halo_fill_kernel<float><<<grid_for(ctx, ctx->n_local), 256, 0, s>>>((float*)h, (float*)u, (float*)v, ctx->d_halo_dst,
+                                                                           ctx->d_halo_src, ctx->d_halo_code,
+                                                                           (const float*)ctx->d_rot, ctx->n_local, mask);
+    ctx->launches++;
+    CS_CUDA(ctx, cudaGetLastError());
+    return CS_OK;
+}
+
+extern "C" int cs_halo_fill_scalar(cs_ctx* ctx, void* field, void* stream) {
+    if (!ctx || !field) return cs_fail(ctx, CS_E_INVALID, "cs_halo_fill_scalar: NULL argument");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return cs_launch_halo(ctx, field, nullptr, nullptr, 1, (cudaStream_t)stream);
+}
+
+extern "C" int cs_halo_fill_vector(cs_ctx* ctx, void* u, void* v, void* stream) {
+    if (!ctx || !u || !v) return cs_fail(ctx, CS_E_INVALID, "cs_halo_fill_vector: NULL argument");
+    if (u == v) return cs_fail(ctx, CS_E_INVALID, "cs_halo_fill_vector: u and v must be distinct arrays");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return cs_launch_halo(ctx, nullptr, u, v, 2, (cudaStream_t)stream);
+}
+
+extern "C" int cs_halo_fill_state(cs_ctx* ctx, void* h, void* u, void* v, void* stream) {
+    if (!ctx || !h || !u || !v) return cs_fail(ctx, CS_E_INVALID, "cs_halo_fill_state: NULL argument");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return cs_launch_halo(ctx, h, u, v, 3, (cudaStream_t)stream);
+}
+
+extern "C" int cs_halo_table_info(const cs_ctx* ctx, size_t cap, int64_t* dst_offset, int64_t* src_offset, int32_t* code,
+                                  size_t* n_ghost) {
+    if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_halo_table_info: NULL context");
+    if (n_ghost) *n_ghost = ctx->halo.size();
+    // local entries first, in the order the fill kernel (and a rotation table) uses, then the remote ones
+    size_t k = 0;
+    for (int pass = 0; pass < 2; ++pass)
+        for (const HaloEntry& e : ctx->halo) {
+            if ((e.src >= 0) != (pass == 0)) continue;
+            if (k < cap) {
+                if (dst_offset) dst_offset[k] = e.dst;
+                if (src_offset) src_offset[k] = e.src;
+                if (code) code[k] = e.code;
+            }
+            ++k;
+        }
+    return CS_OK;
+}
+
+extern "C" int cs_halo_set_rotation(cs_ctx* ctx, const double* rot, size_t n_ghost) {
+    if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_halo_set_rotation: NULL context");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_CUDA(ctx, cudaDeviceSynchronize());
+    if (ctx->d_rot) cudaFree(ctx->d_rot), ctx->d_rot = nullptr;
+    if (!rot) return CS_OK;
+    if (n_ghost != (size_t)ctx->n_local)
+        return cs_fail(ctx, CS_E_INVALID, "rotation table has %zu entries, the context has %lld local ghost cells", n_ghost,
+                       (long long)ctx->n_local);
+    const size_t count = n_ghost * 4;
+    if (cudaMalloc(&ctx->d_rot, count * ctx->esize) != cudaSuccess) return cs_fail(ctx, CS_E_NOMEM, "cudaMalloc of rotation table failed");
+    if (ctx->dtype == CS_F64) {
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_rot, rot, count * 8, cudaMemcpyHostToDevice));
+    } else {
+        std::vector<float> tmp(rot, rot + count);
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_rot, tmp.data(), count * 4, cudaMemcpyHostToDevice));
+    }
+    return CS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// sharded exchange
+// ---------------------------------------------------------------------------------------------
+
+namespace {
+int upload_offsets(cs_ctx* ctx, bool send, int64_t** d_off) {
+    std::vector<int64_t> off(ctx->peers.size() + 1, 0);
+    for (size_t r = 0; r < ctx->peers.size(); ++r)
+        off[r + 1] = off[r] + (send ? ctx->peers[r].send_count : ctx->peers[r].recv_count);
+    if (*d_off) cudaFree(*d_off), *d_off = nullptr;
+    if (cudaMalloc((void**)d_off, off.size() * sizeof(int64_t)) != cudaSuccess)
+        return cs_fail(ctx, CS_E_NOMEM, "cudaMalloc of peer offsets failed");
+    CS_CUDA(ctx, cudaMemcpy(*d_off, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+    return CS_OK;
+}
+}  // namespace
+
+extern "C" int cs_halo_plan(cs_ctx* ctx, int n_peers, const int32_t* peer_tile_begin, const int32_t* peer_tile_count,
+                            int64_t* send_counts, int64_t* recv_counts) {
+    if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_halo_plan: NULL context");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = cs_build_peer_plan(ctx, n_peers, peer_tile_begin, peer_tile_count);
+    if (rc) return rc;
+    if ((rc = upload_offsets(ctx, true, &ctx->d_send_off))) return rc;
+    if ((rc = upload_offsets(ctx, false, &ctx->d_recv_off))) return rc;
+    for (int r = 0; r < n_peers; ++r) {
+        if (send_counts) send_counts[r] = ctx->peers[r].send_count;
+        if (recv_counts) recv_counts[r] = ctx->peers[r].recv_count;
+    }
+    return CS_OK;
+}
+
+int cs_launch_pack(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* sendbuf, cudaStream_t s) {
+    if (ctx->send_total == 0) return CS_OK;
+    const int np = (int)ctx->peers.size();
+    if (ctx->dtype == CS_F64)
+        halo_pack_kernel<double><<<grid_for(ctx, ctx->send_total), 256, 0, s>>>((const double*)h, (const double*)u, (const double*)v,
+                                                                               ctx->d_send_src, (double*)sendbuf, ctx->d_send_off, np,
+                                                                               ctx->send_total, nfields);
+    else
+        halo_pack_kernel<float><<<grid_for(ctx, ctx->send_total), 256, 0, s>>>((const float*)h, (const float*)u, (const float*)v,
+                                                                              ctx->d_send_src, (float*)sendbuf, ctx->d_send_off, np,
+                                                                              ctx->send_total, nfields);
+    ctx->launches++;
+    CS_CUDA(ctx, cudaGetLastError());
+    return CS_OK;
+}
+
+int cs_launch_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u, void* v, int nfields, cudaStream_t s) {
+    if (ctx->recv_total == 0) return CS_OK;
+    const int np = (int)ctx->peers.size();
+    if (ctx->dtype == CS_F64)
+        halo_unpack_kernel<double><<<grid_for(ctx, ctx->recv_total), 256, 0, s>>>((double*)h, (double*)u, (double*)v, ctx->d_recv_dst,
+                                                                                 ctx->d_recv_code, (const double*)recvbuf, ctx->d_recv_off,
+                                                                                 np, ctx->recv_total, nfields);
+    else
+        halo_unpack_kernel<float><<<grid_for(ctx, ctx->recv_total), 256, 0, s>>>((float*)h, (float*)u, (float*)v, ctx->d_recv_dst,
+                                                                                ctx->d_recv_code, (const float*)recvbuf, ctx->d_recv_off, np,
+                                                                                ctx->recv_total, nfields);
+    ctx->launches++;
+    CS_CUDA(ctx, cudaGetLastError());
+    return CS_OK;
+}
+
+extern "C" int cs_halo_pack(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* sendbuf, void* stream) {
+    if (!ctx || !h || !sendbuf || (nfields == 3 && (!u || !v))) return cs_fail(ctx, CS_E_INVALID, "cs_halo_pack: NULL argument");
+    if (nfields != 1 && nfields != 3) return cs_fail(ctx, CS_E_INVALID, "cs_halo_pack: nfields must be 1 or 3");
+    if (ctx->peers.empty()) return cs_fail(ctx, CS_E_INVALID, "cs_halo_pack: call cs_halo_plan first");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return cs_launch_pack(ctx, h, u, v, nfields, sendbuf, (cudaStream_t)stream);
+}
+
+extern "C" int cs_halo_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u, void* v, int nfields, void* stream) {
+    if (!ctx || !h || !recvbuf || (nfields == 3 && (!u || !v))) return cs_fail(ctx, CS_E_INVALID, "cs_halo_unpack: NULL argument");
+    if (nfields != 1 && nfields != 3) return cs_fail(ctx, CS_E_INVALID, "cs_halo_unpack: nfields must be 1 or 3");
+    if (ctx->peers.empty()) return cs_fail(ctx, CS_E_INVALID, "cs_halo_unpack: call cs_halo_plan first");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return cs_launch_unpack(ctx, recvbuf, h, u, v, nfields, (cudaStream_t)stream);
+}

@@ -1,0 +1,108 @@
+// Internal declarations shared by the translation units of libcubesphere_b200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "cubesphere.h"
+
+#define CS_MAX_HALO 4
+
+struct HaloEntry {           // one ghost cell
+    int64_t dst;             // element offset in the local shard
+    int64_t src;             // element offset in the local shard, or -1 when remote
+    int32_t src_tile;        // global tile id of the source
+    int32_t src_local;       // element offset inside the source tile
+    int32_t code;            // bit0 swap, bit1 negate out-u, bit2 negate out-v
+};
+
+struct PeerPlan {
+    int32_t tile_begin = 0, tile_count = 0;
+    int64_t send_count = 0, recv_count = 0;      // cells
+    int64_t send_offset = 0, recv_offset = 0;    // cells, prefix sums over peers
+};
+
+struct cs_ctx {
+    cs_config cfg;
+    int N = 0, p = 0, n = 0, g = 0, m = 0;
+    int T_all = 0, t0 = 0, T = 0;
+    int dtype = CS_F64;
+    size_t esize = 8;
+    int device = 0, num_sms = 148;
+    size_t field_elems = 0;                      // T * m * m
+    bool pitch16 = false;                        // row pitch is a multiple of 16 bytes
+    double radius, omega, gravity, axis[3];
+    double delta;
+    double cf[6][3];                             // Coriolis: sin(lat_rot) = (c0 + c1 X + c2 Y) / rho
+    std::vector<double> xt;                      // face-level periodic tangent table, N + 2g entries
+
+    // device tables (in the state's dtype)
+    void* d_xt = nullptr;                        // X at padded face-level index
+    void* d_ainv = nullptr;                      // 1 / (1 + X^2)
+    double* d_xt64 = nullptr;                    // fp64 copy of d_xt for the diagnostics
+
+    // ghost cells
+    std::vector<HaloEntry> halo;                 // all ghost cells of the owned tiles
+    int64_t n_local = 0;                         // entries with src >= 0
+    int32_t* d_halo_dst = nullptr;               // [n_local]
+    int32_t* d_halo_src = nullptr;
+    uint8_t* d_halo_code = nullptr;
+    void* d_rot = nullptr;                       // optional [n_local][4] rotation (state dtype)
+    int4* d_push = nullptr;                      // [T][4] (dst local tile or -1, dst edge, reverse, code)
+    bool push_complete = false;                  // every neighbour tile is local
+
+    // sharded exchange
+    std::vector<PeerPlan> peers;
+    int64_t send_total = 0, recv_total = 0;
+    int32_t* d_send_src = nullptr;               // [send_total] element offsets to gather
+    int32_t* d_recv_dst = nullptr;               // [recv_total]
+    uint8_t* d_recv_code = nullptr;
+    int64_t* d_send_off = nullptr;               // [n_peers + 1] prefix sums, cells
+    int64_t* d_recv_off = nullptr;
+
+    // scratch state for the RK stages and topography
+    void* qa[3] = {nullptr, nullptr, nullptr};
+    void* qb[3] = {nullptr, nullptr, nullptr};
+    void* topo = nullptr;
+    void* host_state[3] = {nullptr, nullptr, nullptr};   // device copy used by cs_step_host
+    bool has_topo = false;
+
+    // reductions
+    double* d_partials = nullptr;                // [partial_cap][2]
+    int partial_cap = 0;
+    double* d_diag = nullptr;                    // [2]
+    unsigned int* d_ticket = nullptr;
+
+    mutable std::string err;
+    int64_t launches = 0;
+};
+
+int cs_fail(const cs_ctx* ctx, int code, const char* fmt, ...);
+
+#define CS_CUDA(ctx, expr)                                                                       \
+    do {                                                                                         \
+        cudaError_t e__ = (expr);                                                                \
+        if (e__ != cudaSuccess)                                                                  \
+            return cs_fail(ctx, CS_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), \
+                           __FILE__, __LINE__);                                                  \
+    } while (0)
+
+// topology (cs_topology.cu)
+struct SeamInfo { int fb, eb, rev, code; };
+SeamInfo cs_seam(int face, int edge);            // edge: 0 N, 1 S, 2 E, 3 W
+void cs_resolve(int face, int64_t J, int64_t I, int N, int* fb, int64_t* Jb, int64_t* Ib, int* code);
+int cs_build_halo(cs_ctx* ctx);
+int cs_build_peer_plan(cs_ctx* ctx, int n_peers, const int32_t* tb, const int32_t* tc);
+
+// kernel launchers (cs_halo.cu, cs_stage.cu, cs_diag.cu)
+int cs_launch_halo(cs_ctx* ctx, void* h, void* u, void* v, int nfields_mask, cudaStream_t s);
+int cs_launch_stage(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3],
+                    double a, double b, double dt, int part, double* diag_out, cudaStream_t s);
+int cs_launch_diag(cs_ctx* ctx, const void* h, const void* u, const void* v, double* out, cudaStream_t s);
+int cs_launch_pack(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* sendbuf,
+                   cudaStream_t s);
+int cs_launch_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u, void* v, int nfields,
+                     cudaStream_t s);

@@ -1,0 +1,138 @@
+"""Equiangular gnomonic cubed-sphere geometry (host side, fp64).
+
+Not in the reference (its "Geometry: Math/Mesh" box, deck slide 6, is not
+shipped); written from the published equiangular metric (Nair, Thomas & Loft
+2005; Ullrich, Jablonowski & van Leer 2010).
+
+Point on face f:  r = a * (n_f + X x_f + Y y_f) / rho,  X = tan(alpha),
+Y = tan(beta), rho^2 = 1 + X^2 + Y^2, alpha, beta in [-pi/4, pi/4].
+
+The metric is the same on every panel and depends on (X, Y) only, so the
+kernels need one 1-D table ``xtab`` of X at cell centres.  Ghost entries are the
+*periodic* continuation ``xtab[g + N + d] = xtab[g + d]``: a ghost cell holds a
+copy of the neighbour's cell, and seen in the unfolded frame that cell's own
+chart coordinates are exactly the periodic continuation (see DESIGN.md,
+"ghost-cell metric").  All ghost-cell quantities the stencil uses (sqrt(G) u^n,
+kinetic energy, potential) are then the neighbour's own values, which makes
+every seam flux single valued and mass conservation exact.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .topology import FACE_FRAMES
+
+EARTH_RADIUS = 6.37122e6      # m
+EARTH_OMEGA = 7.292e-5        # 1/s
+EARTH_GRAVITY = 9.80616       # m/s^2
+
+
+def centre_tangents(N: int) -> np.ndarray:
+    """X_i = tan(alpha_i), alpha_i = -pi/4 + (i + 1/2) pi/(2N); exactly antisymmetric."""
+    i = np.arange(N, dtype=np.float64)
+    x = np.tan(-0.25 * np.pi + (i + 0.5) * (0.5 * np.pi / N))
+    half = N // 2
+    x[:half] = -x[::-1][:half]
+    if N % 2:
+        x[half] = 0.0
+    return x
+
+
+def padded_tangents(N: int, g: int, lo: int = 0, n: int | None = None) -> np.ndarray:
+    """Periodic continuation of :func:`centre_tangents` for the tile starting at
+    face-level index ``lo`` with ``n`` interior cells (whole face by default)."""
+    n = N if n is None else n
+    x = centre_tangents(N)
+    idx = (lo + np.arange(-g, n + g)) % N
+    return x[idx]
+
+
+def metric_terms(X, Y, a=EARTH_RADIUS):
+    """Point-wise metric terms from broadcastable X, Y (the oracle's definition).
+
+    Returns dict with sg = sqrt(G), covariant g11, g12, g22 and contravariant
+    gi11, gi12, gi22, plus c = a^2 (1+X^2)(1+Y^2) / rho^4 (so f sqrt(G) = f_num c).
+    """
+    A = 1.0 + X * X
+    B = 1.0 + Y * Y
+    rho2 = A + Y * Y
+    r2inv = 1.0 / rho2
+    c = (a * a) * A * B * (r2inv * r2inv)
+    sg = c * np.sqrt(rho2)
+    ia2 = 1.0 / (a * a)
+    return dict(
+        sg=sg, c=c, rho2=rho2,
+        g11=c * A, g12=-(c * X) * Y, g22=c * B,
+        gi11=(rho2 * ia2) / A, gi12=((rho2 * ia2) * (X * Y)) / (A * B), gi22=(rho2 * ia2) / B,
+    )
+
+
+def face_points(N: int, g: int = 0):
+    """Unit position vectors of cell centres, shape [6, N+2g, N+2g, 3].
+
+    Ghost entries (g > 0) use the *extended* chart of the face (alpha beyond
+    +-pi/4), which is only meant for plotting/diagnostics; initial conditions are
+    sampled at interior cells and ghosts are filled by the halo exchange.
+    """
+    i = np.arange(-g, N + g, dtype=np.float64)
+    t = np.tan(-0.25 * np.pi + (i + 0.5) * (0.5 * np.pi / N))
+    if g == 0:
+        t = centre_tangents(N)
+    X, Y = np.meshgrid(t, t, indexing="xy")      # X varies along axis 1 (i), Y along axis 0 (j)
+    out = np.empty((6,) + X.shape + (3,), dtype=np.float64)
+    for f, (nrm, ex, ey) in enumerate(FACE_FRAMES):
+        nrm, ex, ey = (np.asarray(v, dtype=np.float64) for v in (nrm, ex, ey))
+        r = nrm[None, None, :] + X[..., None] * ex + Y[..., None] * ey
+        out[f] = r / np.linalg.norm(r, axis=-1, keepdims=True)
+    return out
+
+
+def lonlat(points):
+    """Longitude in [0, 2 pi) and latitude from unit vectors [..., 3]."""
+    lon = np.mod(np.arctan2(points[..., 1], points[..., 0]), 2.0 * np.pi)
+    lat = np.arcsin(np.clip(points[..., 2], -1.0, 1.0))
+    return lon, lat
+
+
+def tangent_basis(N: int, a=EARTH_RADIUS):
+    """d r / d alpha and d r / d beta at interior cell centres: two arrays [6, N, N, 3]."""
+    t = centre_tangents(N)
+    X, Y = np.meshgrid(t, t, indexing="xy")
+    rho = np.sqrt(1.0 + X * X + Y * Y)
+    e_a = np.empty((6, N, N, 3))
+    e_b = np.empty((6, N, N, 3))
+    for f, (nrm, ex, ey) in enumerate(FACE_FRAMES):
+        nrm, ex, ey = (np.asarray(v, dtype=np.float64) for v in (nrm, ex, ey))
+        P = nrm + X[..., None] * ex + Y[..., None] * ey            # un-normalised position
+        e_a[f] = a * (1.0 + X * X)[..., None] * (ex / rho[..., None] - P * (X / rho ** 3)[..., None])
+        e_b[f] = a * (1.0 + Y * Y)[..., None] * (ey / rho[..., None] - P * (Y / rho ** 3)[..., None])
+    return e_a, e_b
+
+
+def contravariant_from_cartesian(V, N: int, a=EARTH_RADIUS):
+    """Panel-local contravariant components (rad/s) of Cartesian velocities V [6, N, N, 3] (m/s)."""
+    e_a, e_b = tangent_basis(N, a)
+    g11 = np.sum(e_a * e_a, -1)
+    g12 = np.sum(e_a * e_b, -1)
+    g22 = np.sum(e_b * e_b, -1)
+    b1 = np.sum(e_a * V, -1)          # covariant components
+    b2 = np.sum(e_b * V, -1)
+    det = g11 * g22 - g12 * g12
+    return (g22 * b1 - g12 * b2) / det, (g11 * b2 - g12 * b1) / det
+
+
+def cartesian_from_lonlat_wind(u_east, v_north, points):
+    """Cartesian velocity from zonal/meridional components at unit points [..., 3]."""
+    lon, lat = lonlat(points)
+    e_lon = np.stack([-np.sin(lon), np.cos(lon), np.zeros_like(lon)], -1)
+    e_lat = np.stack([-np.sin(lat) * np.cos(lon), -np.sin(lat) * np.sin(lon), np.cos(lat)], -1)
+    return u_east[..., None] * e_lon + v_north[..., None] * e_lat
+
+
+def coriolis_coefficients(axis=(0.0, 0.0, 1.0)) -> np.ndarray:
+    """Per-face (c0, c1, c2) with sin(lat_rot) = (c0 + c1 X + c2 Y) / rho; shape [6, 3].
+
+    ``axis`` is the unit rotation axis (tilted for the rotated Williamson cases).
+    """
+    axis = np.asarray(axis, dtype=np.float64)
+    return np.array([[axis @ np.asarray(v, dtype=np.float64) for v in frame] for frame in FACE_FRAMES])
