@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: explicit time steps of the cubed-sphere shallow-water solver.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one full SSP-RK3 time step (3 fused stage launches, halo fill, all three variables)
+of the Galewsky barotropic-instability case at C1536 in fp32 -- the configuration
+BASELINE.json's target is quoted on -- with synthetic (analytic) initial data.  The metric is
+cell-updates/s = 6 N^2 x steps / seconds.  With N > 1 GPUs (launched by torchrun, one rank per
+GPU) the sphere grows with the GPU count (weak scaling: C1536 / C2176 / C3072 / C4352 for
+1 / 2 / 4 / 8 GPUs, 6 p^2 tiles block-partitioned over the ranks) and halos cross NVLink.
+
+One JSON line is printed by rank 0; see DESIGN.md section 6 for what each key means.
+`--impl reference` times the CPU oracle (the clean-room restatement; the upstream repository has
+no runnable solver) with all host threads on the same workload, one step per "step".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+PKG = ROOT / "sharding-the-sphere-fall-2025-jax-devlab-examples_b200"
+for p in (str(PKG), str(ROOT)):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+WEAK_N = {1: 1536, 2: 2176, 4: 3072, 8: 4352}
+WEAK_P = {1: 1, 2: 1, 4: 2, 8: 2}
+METRIC = "cell_updates_per_s"
+UNIT = "cell-updates/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--N", type=int, default=0, help="cells per face edge (default: weak-scaling table)")
+    ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--case", default="galewsky")
+    ap.add_argument("--kernel", default="auto")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the fp64 side measurement")
+    return ap.parse_args()
+
+
+def measured_peak_gbs():
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        try:
+            return float(json.loads(f.read_text())["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi SM clock / throttle-reason samples during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        mhz, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            try:
+                mhz.append(float(s[0]))
+                mx = max(mx, float(s[1]))
+                for nm, val in zip(names, s[2:6]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(mhz)) if mhz else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(mhz)}
+
+
+def initial_state(case_name, N):
+    """Interior fields [6, N, N] fp64 of the named case, plus the Case object."""
+    from cubesphere import cases
+    case = cases.make_case(case_name, N)
+    return case, cases.stable_dt(case, 0.5)
+
+
+def faces_to_padded_tiles(field, p, g, dtype):
+    """[6, N, N] interior -> [6 p^2, n + 2g, n + 2g] tiles with zero ghosts."""
+    N = field.shape[-1]
+    n = N // p
+    out = np.zeros((6 * p * p, n + 2 * g, n + 2 * g), dtype=dtype)
+    for f in range(6):
+        for ty in range(p):
+            for tx in range(p):
+                out[f * p * p + ty * p + tx, g:g + n, g:g + n] = field[f, ty * n:(ty + 1) * n, tx * n:(tx + 1) * n]
+    return out
+
+
+# ----------------------------------------------------------------------------
+# CPU arm (oracle; bench.py's cpu_baseline leg and the --impl reference arm)
+# ----------------------------------------------------------------------------
+
+def cpu_run(case, dt, steps, warmup):
+    """Time `steps` steps of the C/OpenMP oracle after `warmup` steps.  Returns (cell-updates/s, threads, seconds)."""
+    from oracle import cs_oracle_c as occ
+    from oracle import cs_oracle_np as orc
+    N, g = case.N, 2
+    hs = None
+    if case.hs is not None:
+        hs = orc.halo_fill_scalar(orc.pad(case.hs, g), g)
+    co = occ.COracle(N, g, axis=case.axis, advect_only=case.advect_only, hs=hs)
+    st = [np.ascontiguousarray(orc.pad(x, g)) for x in (case.h, case.u1, case.u2)]
+    occ.halo_fill(N, g, st[0], st[1], st[2])
+    if warmup:
+        co.step(*st, dt, warmup)
+    t0 = time.perf_counter()
+    co.step(*st, dt, steps)
+    sec = time.perf_counter() - t0
+    return 6.0 * N * N * steps / sec, co.threads, sec
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    N = args.N or WEAK_N.get(args.gpus, 1536)
+    case, dt = initial_state(args.case, N)
+    val, threads, sec = cpu_run(case, dt, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{args.case} C{N}, SSP-RK3, one time step per step, CPU oracle (C + OpenMP, fp64)"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{args.steps} full steps of C{N} after {args.warmup} warm-up"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from cubesphere import api, sharded
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE = {world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    N = args.N or WEAK_N.get(world, 1536)
+    p = WEAK_P.get(world, 1) if not args.N else (2 if world > 2 else 1)
+    g = 2
+    tdtype = torch.float32 if args.dtype == "f32" else torch.float64
+    ndtype = np.float32 if args.dtype == "f32" else np.float64
+    esize = 4 if args.dtype == "f32" else 8
+    case, dt = initial_state(args.case, N)
+    stepper = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
+                                     advect_only=case.advect_only, device=local, rank=rank, world=world,
+                                     kernel=args.kernel)
+    t0, tc = stepper.tile_begin, stepper.tile_count
+    host = [faces_to_padded_tiles(x, p, g, ndtype)[t0:t0 + tc] for x in (case.h, case.u1, case.u2)]
+    pinned = [torch.from_numpy(x).pin_memory() for x in host]
+    dev = [x.cuda(non_blocking=True) for x in pinned]
+    if case.hs is not None:
+        stepper.set_topography(torch.from_numpy(faces_to_padded_tiles(case.hs, p, g, ndtype)[t0:t0 + tc]).cuda())
+    stepper.halo_fill(*dev)
+    cells_total = 6.0 * N * N
+    cells_local = float(tc) * stepper.n * stepper.n
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput ------------------------------------------------------
+    for _ in range(args.warmup):
+        stepper.step(*dev, dt)
+    barrier()
+    l0 = stepper.launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        ev0.record()
+        for _ in range(args.steps):
+            stepper.step(*dev, dt)
+        ev1.record()
+        barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = stepper.launches - l0
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = cells_total * args.steps / (ms * 1e-3)
+    finite = bool(torch.isfinite(dev[0]).all().item())
+
+    # ---- roofline of the dominant kernel (fused RK stage), timed per launch ------------------
+    peak, peak_kind = measured_peak_gbs()
+    roof = stepper.time_stage_kernel(dev, dt, reps=max(3, min(args.steps, 10)))
+    words = {True: 6, False: 9}                    # stage 1 reads qs, writes out; later stages also read q0
+    alg_bytes = sum(words[a == 0.0] for a in roof["a"]) * esize * cells_local
+    achieved = alg_bytes / (sum(roof["ms"]) * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_kind": peak_kind, "kernel": roof["kernel"],
+                "algorithmic_bytes_per_cell_step": 24 * esize,
+                "stage_ms": [float(x) for x in roof["ms"]], "frac_of_nominal_8TBs": achieved / 8000.0}
+
+    # ---- end to end through the host-buffer entry point ---------------------------------------
+    e2e = None
+    if world == 1:
+        ctx = stepper.ctx
+        n_e2e = max(3, min(args.steps, 5))
+        ctx.step_host(*pinned, dt, nsteps=1, copy_back=False)            # warm-up (allocates the device copy)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n_e2e):
+            ctx.step_host(*pinned, dt, nsteps=1, copy_back=False)        # H2D state, step, D2H [mass, energy]
+        e1.record()
+        torch.cuda.synchronize()
+        ms_a = e0.elapsed_time(e1) / n_e2e
+        e0.record()
+        for _ in range(n_e2e):
+            ctx.step_host(*pinned, dt, nsteps=1, copy_back=True)         # ... and the whole state back
+        e1.record()
+        torch.cuda.synchronize()
+        ms_b = e0.elapsed_time(e1) / n_e2e
+        nbytes = sum(x.numel() * x.element_size() for x in pinned)
+        e2e = {"value": cells_total / (ms_a * 1e-3), "unit": UNIT, "h2d_bytes_per_step": nbytes,
+               "d2h_bytes_per_step": 16, "ms_per_step": ms_a,
+               "round_trip": {"value": cells_total / (ms_b * 1e-3), "h2d_bytes_per_step": nbytes,
+                              "d2h_bytes_per_step": nbytes + 16, "ms_per_step": ms_b}}
+    else:
+        e2e = stepper.time_e2e(pinned, dev, dt, max(3, min(args.steps, 5)), cells_total)
+
+    # ---- fp64 side measurement (the metric is quoted for fp64 and fp32) ------------------------
+    secondary = None
+    if world == 1 and args.dtype == "f32" and not args.no_secondary:
+        del dev
+        torch.cuda.empty_cache()
+        st64 = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis,
+                                      advect_only=case.advect_only, device=local, rank=0, world=1, kernel=args.kernel)
+        d64 = [torch.from_numpy(faces_to_padded_tiles(x, p, g, np.float64)).cuda() for x in (case.h, case.u1, case.u2)]
+        st64.halo_fill(*d64)
+        for _ in range(args.warmup):
+            st64.step(*d64, dt)
+        torch.cuda.synchronize()
+        ev0.record()
+        for _ in range(args.steps):
+            st64.step(*d64, dt)
+        ev1.record()
+        torch.cuda.synchronize()
+        ms64 = ev0.elapsed_time(ev1)
+        r64 = st64.time_stage_kernel(d64, dt, reps=3)
+        ach64 = sum(words[a == 0.0] for a in r64["a"]) * 8 * cells_local / (sum(r64["ms"]) * 1e-3) / 1e9
+        secondary = {"dtype": "f64", "value": cells_total * args.steps / (ms64 * 1e-3), "unit": UNIT,
+                     "ms_per_step": ms64 / args.steps, "roofline_frac": ach64 / peak, "achieved_GBps": ach64}
+        del d64, st64
+
+    # ---- CPU baseline on rank 0 (bounded sample of the same workload) --------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            nsample = 3
+            val, threads, sec = cpu_run(case, dt, nsample, 1)
+            cpu = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": f"{nsample} full fp64 steps of {args.case} C{N} after 1 warm-up, C + OpenMP oracle ({sec:.1f} s)"}
+        except Exception as exc:  # pragma: no cover
+            cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {exc}"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": f"{args.case} C{N}, SSP-RK3 (3 fused stages + halo) per step, {args.dtype}",
+                       "N": N, "tiles_per_edge": p, "halo": g, "tiles_per_gpu": tc, "parallelism": f"tiles/{world}",
+                       "l2": "state (3 x %.0f MB x 3 buffers per GPU) is larger than L2; no flush needed" %
+                             (cells_local * esize / 1e6),
+                       "finite": finite},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clk.summary(),
+        }
+        if secondary:
+            line["fp64"] = secondary
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,161 @@
+"""One-process-per-GPU driver of the step over a block partition of the tiles.
+
+world == 1: every tile lives on one device and the whole step is ``cs_step`` (halo included).
+world  > 1: each rank owns ``6 p^2 / world`` consecutive tiles.  Per RK stage
+
+    rim cells   (those a peer's ghosts depend on)  -> stage kernel, part 1
+    pack        boundary cells peers need           -> one kernel
+    all-to-all  NCCL over NVLink, on a side stream   } overlapped with
+    inner cells                                     -> stage kernel, part 0  }
+    local ghosts (same-rank neighbours)             -> halo kernel
+    unpack      received cells into remote ghosts   -> one kernel
+
+The partition is the reference's: axis 0 block-sharded over a 1-D mesh
+(reference JAX-DevLab-Examples.py:40-57, 77-79).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import api, topology
+from .partition import block_ranges
+
+RK_PAIRS = {
+    "euler": ((0.0, 1.0),),
+    "ssprk2": ((0.0, 1.0), (0.5, 0.5)),
+    "ssprk3": ((0.0, 1.0), (0.75, 0.25), (1.0 - 2.0 / 3.0, 2.0 / 3.0)),
+}
+
+
+class ShardedStepper:
+    def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f32", rk="ssprk3", limiter="mc", advect_only=False,
+                 axis=(0.0, 0.0, 1.0), device=0, rank=0, world=1, kernel="auto", tangents=None, overlap=True,
+                 group=None):
+        self.rank, self.world, self.rk, self.overlap, self.group = rank, world, rk, overlap, group
+        self.ranges = block_ranges(topology.num_tiles(tiles_per_edge), world)
+        self.tile_begin, self.tile_count = self.ranges[rank]
+        self.ctx = api.Context(N, tiles_per_edge=tiles_per_edge, halo=halo, dtype=dtype, rk=rk, limiter=limiter,
+                               advect_only=advect_only, axis=axis, device=device, kernel=kernel, tangents=tangents,
+                               tile_begin=self.tile_begin, tile_count=self.tile_count if world > 1 else 0)
+        self.n, self.m, self.device = self.ctx.n, self.ctx.m, device
+        self._scratch = None
+        self._extra_launches = 0
+        if world > 1:
+            self.send_counts, self.recv_counts = self.ctx.halo_plan([b for b, _ in self.ranges],
+                                                                    [c for _, c in self.ranges])
+            dev = f"cuda:{device}"
+            self.sendbuf = torch.zeros(max(1, 3 * sum(self.send_counts)), dtype=self.ctx.dtype, device=dev)
+            self.recvbuf = torch.zeros(max(1, 3 * sum(self.recv_counts)), dtype=self.ctx.dtype, device=dev)
+            self.comm_stream = torch.cuda.Stream(device=device)
+            self.qa = [self.ctx.new_field() for _ in range(3)]
+            self.qb = [self.ctx.new_field() for _ in range(3)]
+            self._diag = torch.zeros(2, dtype=torch.float64, device=dev)
+
+    # -- bookkeeping ------------------------------------------------------------------------
+    @property
+    def launches(self):
+        return self.ctx.launches + self._extra_launches
+
+    def close(self):
+        self.ctx.close()
+
+    # -- halo -------------------------------------------------------------------------------
+    def _exchange(self, h, u, v, nfields=3):
+        """pack -> all-to-all -> unpack on the current stream (remote ghosts only)."""
+        self.ctx.halo_pack(h, u, v, self.sendbuf, nfields)
+        ns = nfields * sum(self.send_counts)
+        nr = nfields * sum(self.recv_counts)
+        dist.all_to_all_single(self.recvbuf[:nr], self.sendbuf[:ns],
+                               output_split_sizes=[nfields * c for c in self.recv_counts],
+                               input_split_sizes=[nfields * c for c in self.send_counts], group=self.group)
+        self.ctx.halo_unpack(self.recvbuf, h, u, v, nfields)
+
+    def halo_fill(self, h, u, v):
+        self.ctx.halo_fill_state(h, u, v)
+        if self.world > 1:
+            self._exchange(h, u, v)
+        return h, u, v
+
+    def set_topography(self, hs):
+        self.ctx.set_topography(hs)
+        if self.world > 1:
+            raise NotImplementedError("topography on sharded runs: fill hs ghosts before sharding")
+
+    # -- step -------------------------------------------------------------------------------
+    def step(self, h, u, v, dt):
+        if self.world == 1:
+            self.ctx.step(h, u, v, dt)
+            return h, u, v
+        q0 = (h, u, v)
+        cur = q0
+        pairs = RK_PAIRS[self.rk]
+        main = torch.cuda.current_stream(self.device)
+        for k, (a, b) in enumerate(pairs):
+            last = k == len(pairs) - 1 and len(pairs) > 1
+            out = q0 if last else (self.qa if k % 2 == 0 else self.qb)
+            if self.overlap:
+                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1)              # rim first
+                self.comm_stream.wait_stream(main)
+                with torch.cuda.stream(self.comm_stream):
+                    self._exchange(*out)
+                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=0)              # inner cells meanwhile
+                self.ctx.halo_fill_state(*out)                                 # same-rank ghosts
+                main.wait_stream(self.comm_stream)
+            else:
+                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=2)
+                self.ctx.halo_fill_state(*out)
+                self._exchange(*out)
+            cur = out
+        if len(pairs) == 1:
+            for x, y in zip(q0, cur):
+                x.copy_(y)
+        return h, u, v
+
+    def diagnostics(self, h, u, v):
+        """[mass, energy] of the whole sphere on every rank (fp64)."""
+        out = self.ctx.diagnostics(h, u, v)
+        if self.world > 1:
+            dist.all_reduce(out, group=self.group)
+        return out
+
+    # -- measurement helpers used by bench.py ---------------------------------------------------
+    def time_stage_kernel(self, state, dt, reps=5):
+        """CUDA-event time of each fused-stage launch alone (all owned cells, no halo)."""
+        if self._scratch is None:
+            self._scratch = [self.ctx.new_field() for _ in range(3)]
+        pairs = RK_PAIRS[self.rk]
+        ms = [0.0] * len(pairs)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for k, (a, b) in enumerate(pairs):
+            self.ctx.rk_stage(state, state, self._scratch, a, b, dt, part=2)   # warm
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(reps):
+                self.ctx.rk_stage(state, state, self._scratch, a, b, dt, part=2)
+            e1.record()
+            torch.cuda.synchronize()
+            ms[k] = e0.elapsed_time(e1) / reps
+        return {"a": [a for a, _ in pairs], "ms": ms, "kernel": "cs stage kernel (fused RK stage)"}
+
+    def time_e2e(self, pinned, dev, dt, nsteps, cells_total):
+        """Sharded end-to-end: per step H2D of the shard from pinned memory, the step, D2H of [mass, energy]."""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for warm in (True, False):
+            if not warm:
+                dist.barrier(group=self.group)
+                torch.cuda.synchronize()
+                e0.record()
+            for _ in range(1 if warm else nsteps):
+                for d, p in zip(dev, pinned):
+                    d.copy_(p, non_blocking=True)
+                self.halo_fill(*dev)
+                self.step(*dev, dt)
+                self.diagnostics(*dev).cpu()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / nsteps], device=f"cuda:{self.device}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        nbytes = sum(x.numel() * x.element_size() for x in pinned)
+        return {"value": cells_total / (float(t.item()) * 1e-3), "unit": "cell-updates/s",
+                "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 16, "ms_per_step": float(t.item())}

@@ -127,7 +127,7 @@ def apply_operations(data, operations: str):
     if operations in ("N", "T"):
         return data
     if operations in ("R", "TR"):
-        return data[..., ::-1]
+        return data.flip(-1) if hasattr(data, "flip") else data[..., ::-1]
     raise ValueError(f"Unknown operation: {operations}")
 
 

@@ -1,0 +1,150 @@
+"""CPU-side checks of the boundary: the shared library loads and exports every symbol the header
+declares (no compute calls without a GPU), fails loudly without CUDA, and the sharded exchange plan
+works over gloo with world_size 2."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from cubesphere import _binding, partition
+from oracle import cs_oracle_np as orc
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_library_exports_every_declared_symbol(built_library):
+    header = (ROOT / "include" / "cubesphere.h").read_text()
+    declared = sorted(set(re.findall(r"^CS_API\s+[\w\s\*]+?\b(cs_\w+)\(", header, flags=re.M)))
+    assert declared == _binding.exported_symbols()            # binding and header list the same entry points
+    for name in declared:
+        assert hasattr(built_library, name), name
+    assert built_library.cs_abi_version() == _binding.CS_ABI_VERSION
+
+
+def test_config_struct_matches_header():
+    header = (ROOT / "include" / "cubesphere.h").read_text()
+    body = re.search(r"typedef struct cs_config \{(.*?)\} cs_config;", header, flags=re.S).group(1)
+    fields = re.findall(r"^\s*(?:const\s+)?(?:int32_t|double|double\*)\s*\*?\s*(\w+)", body, flags=re.M)
+    assert fields == [f[0] for f in _binding.CsConfig._fields_]
+
+
+def test_no_cpu_fallback(built_library):
+    """Without a CUDA device context creation fails with CS_E_CUDA and a clear message."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    cfg = _binding.CsConfig()
+    cfg.abi_version, cfg.N, cfg.tiles_per_edge, cfg.halo, cfg.dtype = 1, 24, 1, 2, _binding.CS_F64
+    cfg.rk, cfg.limiter = 3, 2
+    h = ctypes.c_void_p()
+    rc = built_library.cs_ctx_create(ctypes.byref(cfg), ctypes.byref(h))
+    assert rc == _binding.CS_E_CUDA and not h.value
+    assert b"no CPU fallback" in built_library.cs_last_error(None)
+    with pytest.raises(RuntimeError):
+        _binding.check(rc)
+    cfg.N = 25
+    cfg.tiles_per_edge = 2                                     # argument errors come first, as ValueError
+    rc = built_library.cs_ctx_create(ctypes.byref(cfg), ctypes.byref(h))
+    assert rc == _binding.CS_E_INVALID
+    with pytest.raises(ValueError):
+        _binding.check(rc)
+
+
+def test_missing_library_is_loud(monkeypatch, tmp_path):
+    monkeypatch.setenv("CUBESPHERE_B200_LIB", str(tmp_path / "nope.so"))
+    monkeypatch.setattr(_binding, "_lib", None)
+    with pytest.raises(RuntimeError, match="no CPU or PyTorch fallback"):
+        _binding.lib()
+    monkeypatch.setattr(_binding, "_lib", None)
+
+
+def test_product_never_imports_oracle():
+    pkg = ROOT / "sharding-the-sphere-fall-2025-jax-devlab-examples_b200"
+    for f in list(pkg.rglob("*.py")) + list(pkg.rglob("*.cu")) + list(pkg.rglob("*.cuh")):
+        text = f.read_text()
+        assert "oracle" not in text.replace("the oracle", "").replace("NumPy oracle", "").lower() or \
+            not re.search(r"^\s*(from|import)\s+oracle|#include\s+\".*oracle", text, flags=re.M), f
+
+
+@pytest.mark.parametrize("N,p,world", [(8, 1, 2), (8, 2, 4), (12, 2, 8), (8, 1, 6)])
+def test_exchange_plan_serial_emulation(N, p, world):
+    """All ranks emulated in one process: local fill + pack/exchange/unpack == face-level oracle fill."""
+    g = 2
+    rng = np.random.default_rng(7)
+    M = N + 2 * g
+    faces = [rng.standard_normal((6, M, M)) for _ in range(3)]
+    ref = [orc.faces_to_tiles(x, p, g) for x in orc.halo_fill_state(*faces, g)]
+    n = N // p
+    tiles = []
+    for x in faces:
+        t = orc.faces_to_tiles(x, p, g)
+        w = np.full_like(t, np.nan)
+        w[:, g:g + n, g:g + n] = t[:, g:g + n, g:g + n]
+        tiles.append(w)
+    ranges = partition.block_ranges(6 * p * p, world)
+    plans = [partition.ExchangePlan(N, p, g, r, ranges) for r in range(world)]
+    shards = [[np.ascontiguousarray(x[b:b + c]) for x in tiles] for b, c in ranges]
+    for r in range(world):
+        for q in range(world):
+            assert plans[r].send_counts[q] == plans[q].recv_counts[r]
+    packed = [pl.pack(sh) for pl, sh in zip(plans, shards)]
+    for r, (pl, sh) in enumerate(zip(plans, shards)):
+        pl.fill_local(sh)
+        pl.unpack([packed[q][r] for q in range(world)], sh)
+        b, c = ranges[r]
+        for got, want in zip(sh, ref):
+            assert np.array_equal(got, want[b:b + c])
+
+
+_GLOO_WORKER = r"""
+import os, sys
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[2])
+import numpy as np, torch, torch.distributed as dist
+from cubesphere import partition
+from oracle import cs_oracle_np as orc
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+N, p, g = 12, 2, 2
+rng = np.random.default_rng(11)
+M = N + 2 * g
+faces = [rng.standard_normal((6, M, M)) for _ in range(3)]
+ref = [orc.faces_to_tiles(x, p, g) for x in orc.halo_fill_state(*faces, g)]
+n = N // p
+ranges = partition.block_ranges(6 * p * p, world)
+b, c = ranges[rank]
+shard = []
+for x in faces:
+    t = orc.faces_to_tiles(x, p, g)[b:b + c]
+    w = np.full_like(t, np.nan); w[:, g:g + n, g:g + n] = t[:, g:g + n, g:g + n]
+    shard.append(np.ascontiguousarray(w))
+plan = partition.ExchangePlan(N, p, g, rank, ranges)
+send = [torch.from_numpy(np.ascontiguousarray(x)) for x in plan.pack(shard)]
+recv = [torch.empty(3, cnt, dtype=torch.float64) for cnt in plan.recv_counts]
+reqs = []
+for q in range(world):
+    if q == rank: continue
+    reqs.append(dist.isend(send[q], q)); reqs.append(dist.irecv(recv[q], q))
+for r in reqs: r.wait()
+plan.fill_local(shard)
+plan.unpack([x.numpy() for x in recv], shard)
+ok = all(np.array_equal(a, w[b:b + c]) for a, w in zip(shard, ref))
+t = torch.tensor([int(ok)]); dist.all_reduce(t, op=dist.ReduceOp.MIN)
+dist.destroy_process_group()
+sys.exit(0 if int(t.item()) == 1 else 1)
+"""
+
+
+def test_exchange_over_gloo_world2(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER)
+    pkg = ROOT / "sharding-the-sphere-fall-2025-jax-devlab-examples_b200"
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29731", str(script), str(pkg), str(ROOT)]
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]

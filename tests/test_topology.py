@@ -1,0 +1,147 @@
+"""Host logic: cube topology against the reference's own table, tiles, sharding validation."""
+import numpy as np
+import pytest
+
+from cubesphere import api, partition, topology
+from oracle import cs_oracle_np as orc
+
+# Golden data from the reference: the 12 seam swaps in 4 stages with their op flags
+# (/root/reference/JAX-DevLab-Examples.py:114-139; identical on slide 9 of the deck).
+REFERENCE_SCHEDULE = (
+    (((0, "N"), (1, "N"), "R"), ((3, "E"), (4, "W"), "N"), ((2, "S"), (5, "E"), "TR")),
+    (((0, "E"), (4, "N"), "T"), ((2, "E"), (3, "W"), "N"), ((1, "S"), (5, "N"), "N")),
+    (((0, "W"), (2, "N"), "TR"), ((1, "W"), (4, "E"), "N"), ((3, "S"), (5, "S"), "R")),
+    (((0, "S"), (3, "N"), "N"), ((1, "E"), (2, "W"), "N"), ((4, "S"), (5, "W"), "T")),
+)
+
+
+def test_schedule_equals_reference_table():
+    assert topology.create_communication_schedule() == REFERENCE_SCHEDULE
+    api.validate_schedule(REFERENCE_SCHEDULE)
+
+
+def test_oracle_adjacency_equals_reference_table():
+    adj = orc.adjacency()
+    for stage in REFERENCE_SCHEDULE:
+        faces = []
+        for (fa, ea), (fb, eb), ops in stage:
+            assert adj[(fa, ea)][:2] == (fb, eb) and adj[(fb, eb)][:2] == (fa, ea)
+            assert orc.op_flag(fa, ea) == ops == orc.op_flag(fb, eb)
+            faces += [fa, fb]
+        assert sorted(faces) == list(range(6))          # perfect matching: no face twice in a stage
+
+
+def test_frames_right_handed_and_seam_maps_inverse():
+    for n, x, y in topology.FACE_FRAMES:
+        assert np.array_equal(np.cross(x, y), n)
+    for f in range(6):
+        for e in topology.EDGES:
+            fb, eb, rev, S = topology.neighbour(f, e)
+            f2, e2, rev2, S2 = topology.neighbour(fb, eb)
+            assert (f2, e2, rev2) == (f, e, rev)
+            assert np.array_equal(S @ S2, np.eye(2, dtype=np.int64))    # there and back is the identity
+            assert abs(np.linalg.det(S)) == 1
+
+
+def test_apply_operations_matches_reference_semantics():
+    d = np.arange(5.0)
+    assert np.array_equal(topology.apply_operations(d, "N"), d)
+    assert np.array_equal(topology.apply_operations(d, "T"), d)
+    assert np.array_equal(topology.apply_operations(d, "R"), d[::-1])
+    assert np.array_equal(topology.apply_operations(d, "TR"), d[::-1])
+    with pytest.raises(ValueError, match="Unknown operation"):
+        topology.apply_operations(d, "X")
+
+
+def test_validate_schedule_rejects_bad_tables():
+    bad = list(map(list, REFERENCE_SCHEDULE))
+    bad[0][0] = ((0, "N"), (1, "N"), "N")               # wrong flag
+    with pytest.raises(ValueError):
+        api.validate_schedule(bad)
+    bad[0][0] = ((0, "N"), (2, "N"), "R")               # not a seam
+    with pytest.raises(ValueError):
+        api.validate_schedule(bad)
+    with pytest.raises(ValueError):
+        api.validate_schedule(REFERENCE_SCHEDULE[:3])   # 9 of 12 seams
+    with pytest.raises(ValueError, match="Unknown operation"):
+        api.validate_schedule(((((0, "N"), (1, "N"), "Q"),),))
+
+
+@pytest.mark.parametrize("N,p,g", [(8, 1, 1), (8, 1, 2), (8, 2, 2), (12, 3, 2), (12, 2, 3)])
+def test_gather_table_equals_oracle_slicing(N, p, g):
+    """Two independent statements of the halo fill: per-cell gather table vs whole-strip slicing."""
+    rng = np.random.default_rng(1)
+    M = N + 2 * g
+    h, u, v = (rng.standard_normal((6, M, M)) for _ in range(3))
+    ho, uo, vo = orc.halo_fill_state(h, u, v, g)
+    tab = topology.build_halo_table(N, p, g)
+    n = N // p
+
+    def tiles(a):
+        t = orc.faces_to_tiles(a, p, g)
+        w = np.full_like(t, np.nan)
+        w[:, g:g + n, g:g + n] = t[:, g:g + n, g:g + n]
+        return w
+
+    ht, ut, vt = tiles(h), tiles(u), tiles(v)
+    s = (tab["src_tile"], tab["src_j"], tab["src_i"])
+    d = (tab["dst_tile"], tab["dst_j"], tab["dst_i"])
+    ht[d] = ht[s]
+    a, b = partition.apply_code(ut[s], vt[s], tab["code"])
+    ut[d], vt[d] = a, b
+    for got, ref in ((ht, ho), (ut, uo), (vt, vo)):
+        assert np.array_equal(got, orc.faces_to_tiles(ref, p, g))
+
+
+def test_reference_helpers_numpy():
+    N, g = 6, 1
+    a = np.arange((N + 2) ** 2, dtype=np.float64).reshape(N + 2, N + 2)
+    assert np.array_equal(api.extract_boundary_data(a, "N", N), a[N, 1:N + 1])
+    assert np.array_equal(api.extract_boundary_data(a, "S", N), a[1, 1:N + 1])
+    assert np.array_equal(api.extract_boundary_data(a, "E", N), a[1:N + 1, N])
+    assert np.array_equal(api.extract_boundary_data(a, "W", N), a[1:N + 1, 1])
+    line = np.full(N, -1.0)
+    for e, sl in (("N", (N + 1, slice(1, N + 1))), ("S", (0, slice(1, N + 1))),
+                  ("E", (slice(1, N + 1), N + 1)), ("W", (slice(1, N + 1), 0))):
+        out = api.set_ghost_data(a, e, line, N)
+        assert np.array_equal(out[sl], line) and out is not a
+        out[sl] = a[sl]
+        assert np.array_equal(out, a)                    # nothing else changed
+    with pytest.raises(ValueError):
+        api.extract_boundary_data(a, "Q", N)
+
+
+def test_setup_sharding_validation():
+    mesh, sh = api.setup_sharding({"parallelization": {"tiles_per_edge": 1, "num_devices": 6, "device_type": "cpu"}})
+    assert mesh.size == 6 and mesh.axis_names == ("tiles",) and sh.tiles_per_device == 1
+    mesh, sh = api.setup_sharding({"parallelization": {}})                       # reference defaults: cpu, 6, 1
+    assert mesh.size == 6
+    mesh, sh = api.setup_sharding({"parallelization": {"tiles_per_edge": 2, "num_devices": 8}})
+    assert sh.num_tiles == 24 and sh.tile_range(3) == (9, 3) and sh.owner(10) == 3
+    with pytest.raises(ValueError, match="exceeds num_tiles"):
+        api.setup_sharding({"parallelization": {"tiles_per_edge": 1, "num_devices": 7}})
+    with pytest.raises(ValueError, match="not evenly divisible"):
+        api.setup_sharding({"parallelization": {"tiles_per_edge": 1, "num_devices": 4}})
+    with pytest.raises(ValueError):
+        api.setup_sharding({"parallelization": {"device_type": "tpu"}})
+
+
+def test_push_descriptors_consistent_with_table():
+    """The (tile, edge) -> (tile, edge, reverse, code) descriptors agree with the gather table."""
+    N, p, g = 12, 2, 2
+    n = N // p
+    desc = topology.edge_push_descriptors(p)
+    tab = topology.build_halo_table(N, p, g)
+    key = {(int(t), int(j), int(i)): (int(st), int(sj), int(si), int(c)) for t, j, i, st, sj, si, c in
+           zip(tab["dst_tile"], tab["dst_j"], tab["dst_i"], tab["src_tile"], tab["src_j"], tab["src_i"], tab["code"])}
+    for t in range(topology.num_tiles(p)):
+        for e, name in enumerate(topology.EDGES):
+            dt_, de, rev, code = (int(x) for x in desc[t, e])
+            for d in range(g):
+                for k in range(n):
+                    sj, si = {"N": (g + n - 1 - d, g + k), "S": (g + d, g + k),
+                              "E": (g + k, g + n - 1 - d), "W": (g + k, g + d)}[name]
+                    kk = n - 1 - k if rev else k
+                    dj, di = {0: (g + n + d, g + kk), 1: (g - 1 - d, g + kk),
+                              2: (g + kk, g + n + d), 3: (g + kk, g - 1 - d)}[de]
+                    assert key[(dt_, dj, di)] == (t, sj, si, code)
