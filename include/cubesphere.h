@@ -225,6 +225,26 @@ CS_API int cs_halo_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u, vo
 CS_API int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3],
                      double a, double b, double dt, int part, void* stream);
 
+/*
+ * Mass and total energy like cs_diagnostics, for callers that cannot allocate device memory and
+ * therefore cannot create a cs_ctx: plugin handlers inside a framework that has reserved the GPU
+ * for its own allocator (under JAX/XLA preallocation a cudaMalloc from a plugin can fail), and
+ * monitoring hooks on latency-critical threads (cudaMalloc / cudaFree lock the device and may wait
+ * for running work).  No counterpart in the reference; no context; calls no cudaMalloc, cudaFree or
+ * any allocating routine.  The caller passes the inputs (h, u, v, optional hs: same layout as the
+ * state, dtype = CS_F32 | CS_F64, for the tile range [tile_begin, tile_begin + tile_count),
+ * tile_count 0 = all) and the output (device double[2]).  radius / gravity 0 select the defaults.
+ * Scratch is a fixed static array inside the library (about 128 KB on every GPU that loads it, kept
+ * until exit): at most 33,554,432 interior cells per call (C1536 whole sphere: 14,155,776), larger
+ * shards return CS_E_INVALID.  The first call on a device resolves the array's address; make that
+ * call before any stream capture on that device.  All calls on a device share the array (it keeps
+ * the last call's partial sums; the ticket counter is cleared on every call), so calls whose
+ * kernels may overlap on the GPU race: serialise them on one stream.
+ */
+CS_API int cs_diagnostics_noalloc(int dtype, int N, int tiles_per_edge, int halo, int tile_begin, int tile_count,
+                                  double radius, double gravity, const void* h, const void* u, const void* v,
+                                  const void* hs, double* out, int device, void* stream);
+
 /* Number of kernels this library has launched on ctx since creation (bench bookkeeping). */
 CS_API int64_t cs_launch_count(const cs_ctx* ctx);
 

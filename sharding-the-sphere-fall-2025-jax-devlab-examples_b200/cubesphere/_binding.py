@@ -55,6 +55,7 @@ _PROTOTYPES = {
     "cs_halo_pack": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP, _VP]),
     "cs_halo_unpack": (C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_launch_count": (C.c_int64, [_VP]),
+    "cs_diagnostics_noalloc": (C.c_int, [C.c_int] * 6 + [C.c_double, C.c_double, _VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
 }
 
 _lib = None
