@@ -55,9 +55,12 @@ template <> CS_HD double cs_rsqrt<double>(double x) {
 #endif
 }
 
-template <typename R> CS_HD R cs_min(R a, R b) { return a < b ? a : b; }
-template <typename R> CS_HD R cs_max(R a, R b) { return a > b ? a : b; }
-template <typename R> CS_HD R cs_abs(R a) { return a < R(0) ? -a : a; }
+CS_HD float cs_min(float a, float b) { return fminf(a, b); }
+CS_HD double cs_min(double a, double b) { return fmin(a, b); }
+CS_HD float cs_max(float a, float b) { return fmaxf(a, b); }
+CS_HD double cs_max(double a, double b) { return fmax(a, b); }
+CS_HD float cs_abs(float a) { return fabsf(a); }
+CS_HD double cs_abs(double a) { return fabs(a); }
 
 // metric at a cell: everything the stencil needs from (X, Y)
 template <typename R>
@@ -101,23 +104,27 @@ CS_HD Derived<R> cs_derive(const Metric<R>& M, R h, R u, R v, R hs, R grav) {
     return D;
 }
 
+// Limited slope from the two one-sided differences.  Written with min / max only:
+//   minmod(x, y, ...) = max(0, min(x, y, ...)) + min(0, max(x, y, ...))
+// (the first term is non-zero only when all arguments are positive, the second only when all are
+// negative), which gives the same value as sign * min(|.|) without compares and selects.
 template <typename R, int LIM>
 CS_HD R cs_slope(R dm, R dp) {
     if (LIM == CS_LIM_NONE) return R(0.5) * (dm + dp);
-    const R am = cs_abs(dm), ap = cs_abs(dp);
-    R mag;
-    if (LIM == CS_LIM_MINMOD) mag = cs_min(am, ap);
-    else mag = cs_min(cs_min(R(2) * am, R(2) * ap), R(0.5) * cs_abs(dm + dp));
-    const bool pos = dm > R(0) && dp > R(0), neg = dm < R(0) && dp < R(0);
-    return pos ? mag : (neg ? -mag : R(0));
+    if (LIM == CS_LIM_MINMOD) return cs_max(R(0), cs_min(dm, dp)) + cs_min(R(0), cs_max(dm, dp));
+    const R a2 = dm + dm, b2 = dp + dp, c = R(0.5) * (dm + dp);
+    return cs_max(R(0), cs_min(cs_min(a2, b2), c)) + cs_min(R(0), cs_max(cs_max(a2, b2), c));
 }
 
-// upwind flux through the face between a left (L) and right (R) cell
+// Upwind flux through the face between a left (L) and right (R) cell:
+//   max(M, 0) hl + min(M, 0) hr  ==  (M (hl + hr) + |M| (hl - hr)) / 2,   M = (mL + mR) / 2.
+// The second form needs no min / max (|.| is a free operand modifier) and is exactly antisymmetric
+// under exchange of the two sides, which keeps seam fluxes single valued.
 template <typename R>
 CS_HD R cs_face_flux(R mL, R mR, R hL, R sL, R hR, R sR) {
-    const R Fm = R(0.5) * (mL + mR);
+    const R Fm = R(0.25) * (mL + mR);
     const R left = hL + R(0.5) * sL, right = hR - R(0.5) * sR;
-    return cs_max(Fm, R(0)) * left + cs_min(Fm, R(0)) * right;
+    return Fm * (left + right) + cs_abs(Fm) * (left - right);
 }
 
 struct TileCoord { int face, ty, tx; };

@@ -1,6 +1,9 @@
 // K2 -- fused Runge-Kutta stage:  out = a q0 + b (qs + dt L(qs)).
 #include "cs_internal.cuh"
 #include "cs_cell.cuh"
+#include "cs_stage_march.cuh"
+
+#include <cstdlib>
 
 namespace {
 
@@ -19,6 +22,35 @@ stage_naive_kernel(const __grid_constant__ StageParams<R> P) {
         if (inner != (P.part == 0)) return;
     }
     cs_stage_cell<R, LIM>(P, t, j, i);
+}
+
+
+// Rim cells only (those within g of a tile edge): what peers' ghosts depend on.  Used for part 1
+// of a split stage, so that the exchange can start while the inner cells are still being computed.
+template <typename R, int LIM>
+__global__ void __launch_bounds__(256)
+stage_rim_kernel(const __grid_constant__ StageParams<R> P) {
+    const int n = P.n, g = P.g;
+    const int per_tile = n * n - (n - 2 * g) * (n - 2 * g);
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= per_tile) return;
+    int j, i;
+    if (idx < 2 * g * n) {            // bottom and top g rows, full width
+        const int r = idx / n;
+        i = idx - r * n;
+        j = r < g ? r : n - 2 * g + r;
+    } else {                          // left and right g columns of the remaining rows
+        const int r = idx - 2 * g * n;
+        const int jj = r / (2 * g), c = r - jj * (2 * g);
+        j = g + jj;
+        i = c < g ? c : n - 2 * g + c;
+    }
+    cs_stage_cell<R, LIM>(P, blockIdx.y, j, i);
+}
+
+int env_int(const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    return v && *v ? std::atoi(v) : dflt;
 }
 
 template <typename R>
@@ -59,15 +91,77 @@ int launch_naive(cs_ctx* ctx, const StageParams<R>& P, cudaStream_t s) {
     return CS_OK;
 }
 
+template <typename R, int LIM>
+int launch_rim(cs_ctx* ctx, const StageParams<R>& P, cudaStream_t s) {
+    const int per_tile = P.n * P.n - (P.n - 2 * P.g) * (P.n - 2 * P.g);
+    dim3 grid((per_tile + 255) / 256, P.T);
+    stage_rim_kernel<R, LIM><<<grid, 256, 0, s>>>(P);
+    ctx->launches++;
+    CS_CUDA(ctx, cudaGetLastError());
+    return CS_OK;
+}
+
+template <typename R, int V, int LIM, int MINB>
+int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_t s) {
+    MarchGeom G;
+    G.xlo = G.ylo = lo, G.xhi = G.yhi = hi;
+    G.rows = env_int("CS_MARCH_ROWS", 32);
+    if (G.rows < 1) G.rows = 1;
+    G.ngroups = P.m / V;
+    G.grp0 = (lo + P.g) / V;
+    const int grp_last = (hi - 1 + P.g) / V;
+    G.nchunks = (grp_last - G.grp0 + 1 + CS_MARCH_OUT_LANES - 1) / CS_MARCH_OUT_LANES;
+    const int warps = CS_MARCH_THREADS / 32;
+    dim3 grid((G.nchunks + warps - 1) / warps, (hi - lo + G.rows - 1) / G.rows, P.T);
+    stage_march_kernel<R, V, LIM, MINB><<<grid, CS_MARCH_THREADS, 0, s>>>(P, G);
+    ctx->launches++;
+    CS_CUDA(ctx, cudaGetLastError());
+    return CS_OK;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <typename R, int LIM>
+int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
+    const int n = P.n, g = P.g;
+    if (part == 1) return launch_rim<R, LIM>(ctx, P, s);
+    const int lo = part == 0 ? g : 0, hi = part == 0 ? n - g : n;
+    if (hi <= lo) return CS_OK;
+    int variant = ctx->cfg.kernel;
+    bool ok16 = aligned16(P.hq) && aligned16(P.uq) && aligned16(P.vq) && aligned16(P.ho) && aligned16(P.uo) && aligned16(P.vo) &&
+                aligned16(P.h0) && aligned16(P.u0) && aligned16(P.v0) && aligned16(P.topo);
+    const bool can_march = ok16 && g >= 2 && (P.m % 2) == 0 && ((size_t)P.m * P.m * sizeof(R)) % 16 == 0;
+    if (variant == CS_KERNEL_AUTO || variant == CS_KERNEL_TMA) variant = can_march ? CS_KERNEL_MARCH : CS_KERNEL_NAIVE;
+    if (variant == CS_KERNEL_MARCH && !can_march)
+        return cs_fail(ctx, CS_E_INVALID, "the marching stage kernel needs 16-byte aligned fields, halo >= 2 and an even row length");
+    if (variant == CS_KERNEL_NAIVE) {
+        if (part == 2) return launch_naive<R, LIM>(ctx, P, s);
+        StageParams<R> Q = P;           // inner cells with the naive kernel: it filters by part
+        return launch_naive<R, LIM>(ctx, Q, s);
+    }
+    const int occ = env_int("CS_MARCH_OCC", 0);
+    if constexpr (sizeof(R) == 4) {
+        const int vec = env_int("CS_MARCH_VEC", 4);
+        if (vec == 4 && P.m % 4 == 0 && ((size_t)P.m * sizeof(R)) % 16 == 0) {
+            if (occ == 3) return launch_march<R, 4, LIM, 3>(ctx, P, lo, hi, s);
+            return launch_march<R, 4, LIM, 2>(ctx, P, lo, hi, s);
+        }
+        return launch_march<R, 2, LIM, 4>(ctx, P, lo, hi, s);
+    } else {
+        if (occ == 3) return launch_march<R, 2, LIM, 3>(ctx, P, lo, hi, s);
+        return launch_march<R, 2, LIM, 2>(ctx, P, lo, hi, s);
+    }
+}
+
 template <typename R>
 int launch_typed(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a, double b,
                  double dt, int part, double* diag_out, cudaStream_t s) {
     StageParams<R> P = make_params<R>(ctx, q0, qs, qout, a, b, dt, part);
     (void)diag_out;
     switch (ctx->cfg.limiter) {
-        case CS_LIM_NONE: return launch_naive<R, CS_LIM_NONE>(ctx, P, s);
-        case CS_LIM_MINMOD: return launch_naive<R, CS_LIM_MINMOD>(ctx, P, s);
-        default: return launch_naive<R, CS_LIM_MC>(ctx, P, s);
+        case CS_LIM_NONE: return launch_lim<R, CS_LIM_NONE>(ctx, P, part, s);
+        case CS_LIM_MINMOD: return launch_lim<R, CS_LIM_MINMOD>(ctx, P, part, s);
+        default: return launch_lim<R, CS_LIM_MC>(ctx, P, part, s);
     }
 }
 

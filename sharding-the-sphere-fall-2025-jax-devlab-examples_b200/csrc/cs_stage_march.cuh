@@ -1,0 +1,289 @@
+// CS_KERNEL_MARCH -- register-marching fused RK stage.
+//
+// A warp owns a strip of 30 column groups (V adjacent cells per thread, one 8/16-byte vector
+// access per variable per row) and marches along y.  Everything a cell shares with its neighbours
+// is computed ONCE by the owning thread and kept in registers:
+//   * y-neighbours come from the sliding window of rows (J-1, J, J+1, J+2) held by the same thread,
+//     the north-face flux of row J becomes the south-face flux of row J+1;
+//   * x-neighbours come from the adjacent lanes by warp shuffles (2 h values, m1, u_2 and the
+//     Bernoulli function per side); lanes 0 and 31 are halo lanes that compute but do not store.
+// No shared memory and no block-level synchronisation; loads for row J+3 are issued before the
+// arithmetic of row J, so each warp keeps about two rows of traffic in flight.
+// HBM traffic per cell is the algorithmic 2V / 3V words plus the strip overlap (4 extra rows per
+// `rows`, 2 of 32 lanes), most of which hits L2.
+#pragma once
+
+#include "cs_cell.cuh"
+
+struct MarchGeom {
+    int xlo, xhi, ylo, yhi;   // interior index ranges [lo, hi) to update
+    int rows;                 // rows per strip
+    int grp0;                 // first column group that contains an output column
+    int ngroups;              // column groups per row (m / V)
+    int nchunks;              // warps along x
+};
+
+template <typename R, int V> struct VecIO;
+template <> struct VecIO<float, 2> {
+    static __device__ __forceinline__ void ld(const float* p, float (&o)[2]) {
+        const float2 t = *reinterpret_cast<const float2*>(p);
+        o[0] = t.x, o[1] = t.y;
+    }
+    static __device__ __forceinline__ void st(float* p, const float (&o)[2]) {
+        *reinterpret_cast<float2*>(p) = make_float2(o[0], o[1]);
+    }
+};
+template <> struct VecIO<float, 4> {
+    static __device__ __forceinline__ void ld(const float* p, float (&o)[4]) {
+        const float4 t = *reinterpret_cast<const float4*>(p);
+        o[0] = t.x, o[1] = t.y, o[2] = t.z, o[3] = t.w;
+    }
+    static __device__ __forceinline__ void st(float* p, const float (&o)[4]) {
+        *reinterpret_cast<float4*>(p) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+};
+template <> struct VecIO<double, 2> {
+    static __device__ __forceinline__ void ld(const double* p, double (&o)[2]) {
+        const double2 t = *reinterpret_cast<const double2*>(p);
+        o[0] = t.x, o[1] = t.y;
+    }
+    static __device__ __forceinline__ void st(double* p, const double (&o)[2]) {
+        *reinterpret_cast<double2*>(p) = make_double2(o[0], o[1]);
+    }
+};
+
+#define CS_MARCH_THREADS 128
+#define CS_MARCH_OUT_LANES 30
+
+// derived quantities of one row segment (V cells) from raw values
+template <typename R, int V>
+struct RowDerived {
+    R m1[V], m2[V], c1[V], c2[V], Bn[V];
+    R isg[V], q[V], fsg[V];   // 1/sqrt(G), rho^2/a^2, f sqrt(G): only used when the row is the output row
+};
+
+// Constants folded once per thread so that the row loop multiplies as little as possible:
+//   kq   = b dt / (2 delta a^2)   (momentum: out = a q0 + b u + kq rho^2 (g^ij-shape) T'),
+//   kisg = b dt / (delta a^2)     (continuity: out = a q0 + b h - isg' (dF + dG)),
+//   kf   = 2 Omega 2 delta        (f sqrt(G) in units of the undivided differences).
+template <typename R, int V>
+struct MarchConst {
+    R a2A[V], cfx[V], Xax[V], ax[V], X[V];
+    R kq, kisg, kf2;   // kf2 = kf * cf[2]
+};
+
+template <typename R, int V>
+__device__ __forceinline__ void march_derive(const StageParams<R>& P, const MarchConst<R, V>& K, R Y, R ay,
+                                             const R (&h)[V], const R (&u)[V], const R (&v)[V], const R (&hs)[V],
+                                             RowDerived<R, V>& D) {
+    const R Y2 = Y * Y, B = R(1) + Y2, ayk = ay * K.kisg, cfy = K.kf2 * Y;
+#pragma unroll
+    for (int c = 0; c < V; ++c) {
+        const R rho2 = K.X[c] * K.X[c] + B;
+        const R rinv = cs_rsqrt<R>(rho2);
+        const R r2 = rinv * rinv;
+        const R cc = (K.a2A[c] * B) * (r2 * r2);
+        const R rho = rho2 * rinv;
+        const R sg = cc * rho;
+        const R g11 = cc * (rho2 - Y2), g22 = cc * B, g12 = -(cc * K.X[c]) * Y;     // 1 + X^2 = rho^2 - Y^2
+        D.m1[c] = sg * u[c];
+        D.m2[c] = sg * v[c];
+        D.c1[c] = g11 * u[c] + g12 * v[c];
+        D.c2[c] = g12 * u[c] + g22 * v[c];
+        const R Kin = R(0.5) * (u[c] * D.c1[c] + v[c] * D.c2[c]);
+        D.Bn[c] = P.grav * (h[c] + hs[c]) + Kin;
+        D.q[c] = rho2 * K.kq;
+        D.isg[c] = (rho2 * rho) * (K.ax[c] * ayk);          // b dt / delta * rho^3 / (a^2 A B)
+        D.fsg[c] = (K.cfx[c] + cfy) * cc;
+    }
+}
+
+template <typename R, int V, int LIM, int MINB>
+__global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
+stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant__ MarchGeom G) {
+    const int lane = threadIdx.x & 31;
+    const int chunk = blockIdx.x * (CS_MARCH_THREADS / 32) + (threadIdx.x >> 5);
+    if (chunk >= G.nchunks) return;                       // whole warp leaves together
+    const int t = blockIdx.z;
+    const int j0 = G.ylo + blockIdx.y * G.rows;
+    const int j1 = min(j0 + G.rows, G.yhi);
+    const int m = P.m, g = P.g;
+    const TileCoord tc = cs_tile_coord(t + P.t0, P.p);
+    const int grp = G.grp0 + chunk * CS_MARCH_OUT_LANES + lane - 1;
+    const bool lane_out = lane >= 1 && lane <= CS_MARCH_OUT_LANES && grp < G.ngroups;
+    const int col0 = min(max(grp, 0), G.ngroups - 1) * V;
+    const R* yt = P.xt + tc.ty * P.n;
+    const R* ayt = P.ainv + tc.ty * P.n;
+    const R* cf = P.cf[tc.face];
+    const bool has_topo = P.topo != nullptr, read_q0 = P.a != R(0);
+
+    MarchConst<R, V> K;
+    bool om[V];
+    bool all_out = true;
+    {
+        const R kf = P.two_omega / P.r2d;
+        K.kq = P.ia2 * P.b * P.dt * P.r2d;
+        K.kisg = P.ia2 * P.b * P.dt * P.rd;
+        K.kf2 = kf * cf[2];
+#pragma unroll
+        for (int c = 0; c < V; ++c) {
+            K.X[c] = P.xt[tc.tx * P.n + col0 + c];
+            K.ax[c] = P.ainv[tc.tx * P.n + col0 + c];
+            K.a2A[c] = P.a2 * (R(1) + K.X[c] * K.X[c]);
+            K.cfx[c] = kf * (cf[0] + cf[1] * K.X[c]);
+            K.Xax[c] = K.X[c] * K.ax[c];
+            const int i = col0 + c - g;
+            om[c] = lane_out && i >= G.xlo && i < G.xhi;
+            all_out = all_out && om[c];
+        }
+    }
+    const size_t tbase = (size_t)t * m * m + col0;
+    using IO = VecIO<R, V>;
+
+    // ---- prologue: rows J0-2 .. J0+1 --------------------------------------------------------
+    const int J0 = j0 + g, J1 = j1 + g;
+    R hc[V], hp[V], nh[V], uc[V], vc[V], nu[V], nv[V], nt[V];
+    R c1m[V], Bnm[V], Gs[V], syc[V];
+    RowDerived<R, V> Dc;
+    {
+        R hmm[V], hm1[V], um[V], vm[V], tm[V], tcur[V];
+        IO::ld(P.hq + tbase + (size_t)(J0 - 2) * m, hmm);
+        IO::ld(P.hq + tbase + (size_t)(J0 - 1) * m, hm1);
+        IO::ld(P.hq + tbase + (size_t)J0 * m, hc);
+        IO::ld(P.hq + tbase + (size_t)(J0 + 1) * m, hp);
+        IO::ld(P.uq + tbase + (size_t)(J0 - 1) * m, um);
+        IO::ld(P.vq + tbase + (size_t)(J0 - 1) * m, vm);
+        IO::ld(P.uq + tbase + (size_t)J0 * m, uc);
+        IO::ld(P.vq + tbase + (size_t)J0 * m, vc);
+#pragma unroll
+        for (int c = 0; c < V; ++c) tm[c] = tcur[c] = nt[c] = R(0);
+        if (has_topo) {
+            IO::ld(P.topo + tbase + (size_t)(J0 - 1) * m, tm);
+            IO::ld(P.topo + tbase + (size_t)J0 * m, tcur);
+            IO::ld(P.topo + tbase + (size_t)(J0 + 1) * m, nt);
+        }
+        IO::ld(P.hq + tbase + (size_t)min(J0 + 2, m - 1) * m, nh);
+        IO::ld(P.uq + tbase + (size_t)(J0 + 1) * m, nu);
+        IO::ld(P.vq + tbase + (size_t)(J0 + 1) * m, nv);
+        RowDerived<R, V> Dm;
+        march_derive<R, V>(P, K, yt[J0 - 1], ayt[J0 - 1], hm1, um, vm, tm, Dm);
+        march_derive<R, V>(P, K, yt[J0], ayt[J0], hc, uc, vc, tcur, Dc);
+#pragma unroll
+        for (int c = 0; c < V; ++c) {
+            const R sym = cs_slope<R, LIM>(hm1[c] - hmm[c], hc[c] - hm1[c]);
+            syc[c] = cs_slope<R, LIM>(hc[c] - hm1[c], hp[c] - hc[c]);
+            Gs[c] = cs_face_flux<R>(Dm.m2[c], Dc.m2[c], hm1[c], sym, hc[c], syc[c]);
+            c1m[c] = Dm.c1[c];
+            Bnm[c] = Dm.Bn[c];
+        }
+    }
+
+    // ---- march ---------------------------------------------------------------------------------
+    // One row per call.  `Dcur` holds the derived quantities of row J, `Dnext` receives those of
+    // row J+1; the loop calls the body twice with the two sets swapped, so they never get copied.
+    auto row = [&](RowDerived<R, V>& Dcur, RowDerived<R, V>& Dnext, const int J) {
+        // loads for the next call (rows J+3 / J+2) and the point-wise q0 of this row
+        R ph[V], pu[V], pv[V], pt[V], q0h[V], q0u[V], q0v[V];
+        const size_t oJ = tbase + (size_t)J * m;
+        const size_t o2 = tbase + (size_t)min(J + 2, m - 1) * m;
+        IO::ld(P.hq + tbase + (size_t)min(J + 3, m - 1) * m, ph);
+        IO::ld(P.uq + o2, pu);
+        IO::ld(P.vq + o2, pv);
+        if (has_topo) IO::ld(P.topo + o2, pt);
+        if (read_q0) {
+            IO::ld(P.h0 + oJ, q0h);
+            IO::ld(P.u0 + oJ, q0u);
+            IO::ld(P.v0 + oJ, q0v);
+        }
+
+        // row J+1: derived quantities, y-slope and the north-face flux of row J
+        march_derive<R, V>(P, K, yt[J + 1], ayt[J + 1], hp, nu, nv, nt, Dnext);
+        R dG[V];
+#pragma unroll
+        for (int c = 0; c < V; ++c) {
+            const R syp = cs_slope<R, LIM>(hp[c] - hc[c], nh[c] - hp[c]);
+            const R Gn = cs_face_flux<R>(Dcur.m2[c], Dnext.m2[c], hc[c], syc[c], hp[c], syp);
+            dG[c] = Gn - Gs[c];
+            Gs[c] = Gn;
+            syc[c] = syp;
+        }
+
+        // row J: x-neighbours from the adjacent lanes
+        R he[V + 4], m1e[V + 2], c2e[V + 2], Bne[V + 2];
+        he[0] = __shfl_up_sync(0xffffffffu, hc[V - 2], 1);
+        he[1] = __shfl_up_sync(0xffffffffu, hc[V - 1], 1);
+        he[V + 2] = __shfl_down_sync(0xffffffffu, hc[0], 1);
+        he[V + 3] = __shfl_down_sync(0xffffffffu, hc[1], 1);
+        m1e[0] = __shfl_up_sync(0xffffffffu, Dcur.m1[V - 1], 1);
+        m1e[V + 1] = __shfl_down_sync(0xffffffffu, Dcur.m1[0], 1);
+        c2e[0] = __shfl_up_sync(0xffffffffu, Dcur.c2[V - 1], 1);
+        c2e[V + 1] = __shfl_down_sync(0xffffffffu, Dcur.c2[0], 1);
+        Bne[0] = __shfl_up_sync(0xffffffffu, Dcur.Bn[V - 1], 1);
+        Bne[V + 1] = __shfl_down_sync(0xffffffffu, Dcur.Bn[0], 1);
+#pragma unroll
+        for (int c = 0; c < V; ++c) {
+            he[c + 2] = hc[c];
+            m1e[c + 1] = Dcur.m1[c];
+            c2e[c + 1] = Dcur.c2[c];
+            Bne[c + 1] = Dcur.Bn[c];
+        }
+        R sxe[V + 2], F[V + 1];
+#pragma unroll
+        for (int k = 0; k < V + 2; ++k) sxe[k] = cs_slope<R, LIM>(he[k + 1] - he[k], he[k + 2] - he[k + 1]);
+#pragma unroll
+        for (int k = 0; k < V + 1; ++k) F[k] = cs_face_flux<R>(m1e[k], m1e[k + 1], he[k + 1], sxe[k], he[k + 2], sxe[k + 1]);
+
+        // tendencies and the RK combination for row J
+        const R ay = ayt[J], Yay = yt[J] * ay;
+        R oh[V], ou[V], ov[V];
+#pragma unroll
+        for (int c = 0; c < V; ++c) {
+            // every factor b, dt, 1/delta, 1/a^2 is already inside isg, q and fsg (MarchConst)
+            oh[c] = P.b * hc[c] - ((F[c + 1] - F[c]) + dG[c]) * Dcur.isg[c];
+            ou[c] = P.b * uc[c];
+            ov[c] = P.b * vc[c];
+            if (!P.advect_only) {
+                const R eta = ((c2e[c + 2] - c2e[c]) - (Dnext.c1[c] - c1m[c])) + Dcur.fsg[c];
+                const R T1 = eta * vc[c] - (Bne[c + 2] - Bne[c]);
+                const R T2 = -eta * uc[c] - (Dnext.Bn[c] - Bnm[c]);
+                const R gi11 = Dcur.q[c] * K.ax[c], gi22 = Dcur.q[c] * ay;
+                const R gi12 = (Dcur.q[c] * K.Xax[c]) * Yay;
+                ou[c] += gi11 * T1 + gi12 * T2;
+                ov[c] += gi12 * T1 + gi22 * T2;
+            }
+            if (read_q0) {
+                oh[c] += P.a * q0h[c];
+                ou[c] += P.a * q0u[c];
+                ov[c] += P.a * q0v[c];
+            }
+        }
+        if (all_out) {
+            IO::st(P.ho + oJ, oh);
+            IO::st(P.uo + oJ, ou);
+            IO::st(P.vo + oJ, ov);
+        } else {
+#pragma unroll
+            for (int c = 0; c < V; ++c)
+                if (om[c]) P.ho[oJ + c] = oh[c], P.uo[oJ + c] = ou[c], P.vo[oJ + c] = ov[c];
+        }
+
+        // slide the raw-row window one row north
+#pragma unroll
+        for (int c = 0; c < V; ++c) {
+            c1m[c] = Dcur.c1[c];
+            Bnm[c] = Dcur.Bn[c];
+            hc[c] = hp[c], hp[c] = nh[c], nh[c] = ph[c];
+            uc[c] = nu[c], vc[c] = nv[c], nu[c] = pu[c], nv[c] = pv[c];
+            if (has_topo) nt[c] = pt[c];
+        }
+    };
+
+    RowDerived<R, V> Dn;
+    int J = J0;
+#pragma unroll 1
+    for (; J + 1 < J1; J += 2) {
+        row(Dc, Dn, J);
+        row(Dn, Dc, J + 1);
+    }
+    if (J < J1) row(Dc, Dn, J);
+}
