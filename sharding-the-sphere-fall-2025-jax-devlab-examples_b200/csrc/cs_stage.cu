@@ -2,6 +2,7 @@
 #include "cs_internal.cuh"
 #include "cs_cell.cuh"
 #include "cs_stage_march.cuh"
+#include "cs_stage_tma.cuh"
 
 #include <cstdlib>
 
@@ -101,11 +102,21 @@ int launch_rim(cs_ctx* ctx, const StageParams<R>& P, cudaStream_t s) {
     return CS_OK;
 }
 
+// Strip height: tall strips amortise the 4-row prologue, short ones keep enough warps in flight
+// on small grids.  Tuned on C1536 (profiles/r01_stage_sweep_*.log); CS_MARCH_ROWS overrides.
+int default_rows(int n, int T, bool f32) {
+    const long long cells = (long long)n * n * T;
+    if (cells >= 8000000) return f32 ? 64 : 32;
+    if (cells >= 500000) return 32;
+    return 16;
+}
+
 template <typename R, int V, int LIM, int MINB>
 int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_t s) {
     MarchGeom G;
     G.xlo = G.ylo = lo, G.xhi = G.yhi = hi;
-    G.rows = env_int("CS_MARCH_ROWS", 32);
+    G.rows = env_int("CS_MARCH_ROWS", default_rows(P.n, P.T, sizeof(R) == 4));
+    G.prefetch = env_int("CS_MARCH_PREFETCH", 2);
     if (G.rows < 1) G.rows = 1;
     G.ngroups = P.m / V;
     G.grp0 = (lo + P.g) / V;
@@ -114,6 +125,34 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStrea
     const int warps = CS_MARCH_THREADS / 32;
     dim3 grid((G.nchunks + warps - 1) / warps, (hi - lo + G.rows - 1) / G.rows, P.T);
     stage_march_kernel<R, V, LIM, MINB><<<grid, CS_MARCH_THREADS, 0, s>>>(P, G);
+    ctx->launches++;
+    CS_CUDA(ctx, cudaGetLastError());
+    return CS_OK;
+}
+
+template <typename R, int V, int LIM, int MINB>
+int launch_tma(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_t s) {
+    MarchGeom G;
+    G.xlo = G.ylo = lo, G.xhi = G.yhi = hi;
+    G.rows = env_int("CS_MARCH_ROWS", 32);
+    G.prefetch = env_int("CS_MARCH_PREFETCH", 4);
+    if (G.rows < 1) G.rows = 1;
+    G.ngroups = P.m / V;
+    G.grp0 = (lo + P.g) / V;
+    const int grp_last = (hi - 1 + P.g) / V;
+    G.nchunks = (grp_last - G.grp0 + 1 + CS_MARCH_OUT_LANES - 1) / CS_MARCH_OUT_LANES;
+    const int warps = CS_MARCH_THREADS / 32;
+    int ring = env_int("CS_TMA_RING", 6);
+    ring = ring < 4 ? 4 : ring > CS_TMA_MAX_RING ? CS_TMA_MAX_RING : ring;
+    const int narr = 3 + (P.a != R(0) ? 3 : 0) + (P.topo ? 1 : 0);
+    const size_t smem = (size_t)warps * ((size_t)ring * narr * cs_tma_astride<R, V>() + CS_TMA_MAX_RING * 8);
+    static size_t configured = 0;     // per instantiation
+    if (smem > configured) {
+        CS_CUDA(ctx, cudaFuncSetAttribute(stage_tma_kernel<R, V, LIM, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    dim3 grid((G.nchunks + warps - 1) / warps, (hi - lo + G.rows - 1) / G.rows, P.T);
+    stage_tma_kernel<R, V, LIM, MINB><<<grid, CS_MARCH_THREADS, smem, s>>>(P, G, ring);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;
@@ -131,13 +170,21 @@ int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
     bool ok16 = aligned16(P.hq) && aligned16(P.uq) && aligned16(P.vq) && aligned16(P.ho) && aligned16(P.uo) && aligned16(P.vo) &&
                 aligned16(P.h0) && aligned16(P.u0) && aligned16(P.v0) && aligned16(P.topo);
     const bool can_march = ok16 && g >= 2 && (P.m % 2) == 0 && ((size_t)P.m * P.m * sizeof(R)) % 16 == 0;
-    if (variant == CS_KERNEL_AUTO || variant == CS_KERNEL_TMA) variant = can_march ? CS_KERNEL_MARCH : CS_KERNEL_NAIVE;
+    const bool can_tma = can_march && ((size_t)P.m * sizeof(R)) % 16 == 0;
+    if (variant == CS_KERNEL_AUTO) variant = can_march ? CS_KERNEL_MARCH : CS_KERNEL_NAIVE;
     if (variant == CS_KERNEL_MARCH && !can_march)
         return cs_fail(ctx, CS_E_INVALID, "the marching stage kernel needs 16-byte aligned fields, halo >= 2 and an even row length");
-    if (variant == CS_KERNEL_NAIVE) {
-        if (part == 2) return launch_naive<R, LIM>(ctx, P, s);
-        StageParams<R> Q = P;           // inner cells with the naive kernel: it filters by part
-        return launch_naive<R, LIM>(ctx, Q, s);
+    if (variant == CS_KERNEL_TMA && !can_tma)
+        return cs_fail(ctx, CS_E_INVALID, "the TMA stage kernel needs 16-byte aligned fields and rows, and halo >= 2");
+    if (variant == CS_KERNEL_NAIVE) return launch_naive<R, LIM>(ctx, P, s);
+    if (variant == CS_KERNEL_TMA) {
+        const int vec = env_int("CS_MARCH_VEC", 0);
+        if constexpr (sizeof(R) == 4) {
+            if (vec != 2 && P.m % 4 == 0) return launch_tma<R, 4, LIM, 2>(ctx, P, lo, hi, s);
+            return launch_tma<R, 2, LIM, 4>(ctx, P, lo, hi, s);
+        } else {
+            return launch_tma<R, 2, LIM, 2>(ctx, P, lo, hi, s);
+        }
     }
     const int occ = env_int("CS_MARCH_OCC", 0);
     if constexpr (sizeof(R) == 4) {

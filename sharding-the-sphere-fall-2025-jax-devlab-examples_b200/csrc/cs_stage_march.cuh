@@ -16,12 +16,15 @@
 #include "cs_cell.cuh"
 
 struct MarchGeom {
+    int prefetch;             // L2 prefetch distance in rows (0 = none)
     int xlo, xhi, ylo, yhi;   // interior index ranges [lo, hi) to update
     int rows;                 // rows per strip
     int grp0;                 // first column group that contains an output column
     int ngroups;              // column groups per row (m / V)
     int nchunks;              // warps along x
 };
+
+__device__ __forceinline__ void march_prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 template <typename R, int V> struct VecIO;
 template <> struct VecIO<float, 2> {
@@ -52,6 +55,11 @@ template <> struct VecIO<double, 2> {
     }
 };
 
+template <> struct VecIO<double, 1> {
+    static __device__ __forceinline__ void ld(const double* p, double (&o)[1]) { o[0] = *p; }
+    static __device__ __forceinline__ void st(double* p, const double (&o)[1]) { *p = o[0]; }
+};
+
 #define CS_MARCH_THREADS 128
 #define CS_MARCH_OUT_LANES 30
 
@@ -61,6 +69,24 @@ struct RowDerived {
     R m1[V], m2[V], c1[V], c2[V], Bn[V];
     R isg[V], q[V], fsg[V];   // 1/sqrt(G), rho^2/a^2, f sqrt(G): only used when the row is the output row
 };
+
+// Half of the limited slope (what the face states need): scaling by 2 is exact, so
+// minmod(dm, dp, (dm + dp) / 4) is bit-identical to cs_slope(dm, dp) / 2.
+template <typename R, int LIM>
+__device__ __forceinline__ R march_half_slope(R dm, R dp) {
+    if (LIM == CS_LIM_NONE) return R(0.25) * (dm + dp);
+    if (LIM == CS_LIM_MINMOD) return R(0.5) * (cs_max(R(0), cs_min(dm, dp)) + cs_min(R(0), cs_max(dm, dp)));
+    const R c = R(0.25) * (dm + dp);
+    return cs_max(R(0), cs_min(cs_min(dm, dp), c)) + cs_min(R(0), cs_max(cs_max(dm, dp), c));
+}
+
+// Four times the upwind face flux (the factor 1/4 is folded into MarchConst::kisg);
+// hsL, hsR are half slopes.
+template <typename R>
+__device__ __forceinline__ R march_flux4(R mL, R mR, R hL, R hsL, R hR, R hsR) {
+    const R M = mL + mR, left = hL + hsL, right = hR - hsR;
+    return M * (left + right) + cs_abs(M) * (left - right);
+}
 
 // Constants folded once per thread so that the row loop multiplies as little as possible:
 //   kq   = b dt / (2 delta a^2)   (momentum: out = a q0 + b u + kq rho^2 (g^ij-shape) T'),
@@ -98,6 +124,67 @@ __device__ __forceinline__ void march_derive(const StageParams<R>& P, const Marc
     }
 }
 
+// x direction, tendencies and RK combination of one row segment (shared by the LDG-fed and the
+// TMA-fed kernels).  Each lane computes the half slopes of its own V cells and the V faces on
+// their left; the neighbour's slope and the right-most face come by shuffle, so no slope or flux
+// is computed twice within a warp (and both sides of a face see one value).
+template <typename R, int V, int LIM>
+__device__ __forceinline__ void march_row_update(const StageParams<R>& P, const MarchConst<R, V>& K,
+                                                 const RowDerived<R, V>& Dcur, const RowDerived<R, V>& Dnext,
+                                                 const R (&hc)[V], const R (&uc)[V], const R (&vc)[V], const R (&dG)[V],
+                                                 const R (&c1m)[V], const R (&Bnm)[V], R Yc, R ayc, bool read_q0,
+                                                 const R (&q0h)[V], const R (&q0u)[V], const R (&q0v)[V],
+                                                 R (&oh)[V], R (&ou)[V], R (&ov)[V]) {
+    const R hl = __shfl_up_sync(0xffffffffu, hc[V - 1], 1);
+    const R hr = __shfl_down_sync(0xffffffffu, hc[0], 1);
+    R sx[V], F[V + 1], c2e[V + 2], Bne[V + 2];
+#pragma unroll
+    for (int c = 0; c < V; ++c) {
+        const R hm_ = c == 0 ? hl : hc[c > 0 ? c - 1 : 0];
+        const R hp_ = c == V - 1 ? hr : hc[c < V - 1 ? c + 1 : V - 1];
+        sx[c] = march_half_slope<R, LIM>(hc[c] - hm_, hp_ - hc[c]);
+    }
+    const R sxl = __shfl_up_sync(0xffffffffu, sx[V - 1], 1);
+    const R m1l = __shfl_up_sync(0xffffffffu, Dcur.m1[V - 1], 1);
+    F[0] = march_flux4<R>(m1l, Dcur.m1[0], hl, sxl, hc[0], sx[0]);
+#pragma unroll
+    for (int c = 1; c < V; ++c) F[c] = march_flux4<R>(Dcur.m1[c - 1], Dcur.m1[c], hc[c - 1], sx[c - 1], hc[c], sx[c]);
+    F[V] = __shfl_down_sync(0xffffffffu, F[0], 1);
+    c2e[0] = __shfl_up_sync(0xffffffffu, Dcur.c2[V - 1], 1);
+    c2e[V + 1] = __shfl_down_sync(0xffffffffu, Dcur.c2[0], 1);
+    Bne[0] = __shfl_up_sync(0xffffffffu, Dcur.Bn[V - 1], 1);
+    Bne[V + 1] = __shfl_down_sync(0xffffffffu, Dcur.Bn[0], 1);
+#pragma unroll
+    for (int c = 0; c < V; ++c) {
+        c2e[c + 1] = Dcur.c2[c];
+        Bne[c + 1] = Dcur.Bn[c];
+    }
+
+// tendencies and the RK combination
+    const R ay = ayc, Yay = Yc * ayc;
+#pragma unroll
+    for (int c = 0; c < V; ++c) {
+        // every factor b, dt, 1/delta, 1/a^2 is already inside isg, q and fsg (MarchConst)
+        oh[c] = P.b * hc[c] - ((F[c + 1] - F[c]) + dG[c]) * Dcur.isg[c];
+        ou[c] = P.b * uc[c];
+        ov[c] = P.b * vc[c];
+        if (!P.advect_only) {
+            const R eta = ((c2e[c + 2] - c2e[c]) - (Dnext.c1[c] - c1m[c])) + Dcur.fsg[c];
+            const R T1 = eta * vc[c] - (Bne[c + 2] - Bne[c]);
+            const R T2 = -eta * uc[c] - (Dnext.Bn[c] - Bnm[c]);
+            const R gi11 = Dcur.q[c] * K.ax[c], gi22 = Dcur.q[c] * ay;
+            const R gi12 = (Dcur.q[c] * K.Xax[c]) * Yay;
+            ou[c] += gi11 * T1 + gi12 * T2;
+            ov[c] += gi12 * T1 + gi22 * T2;
+        }
+        if (read_q0) {
+            oh[c] += P.a * q0h[c];
+            ou[c] += P.a * q0u[c];
+            ov[c] += P.a * q0v[c];
+        }
+    }
+}
+
 template <typename R, int V, int LIM, int MINB>
 __global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
 stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant__ MarchGeom G) {
@@ -123,7 +210,7 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     {
         const R kf = P.two_omega / P.r2d;
         K.kq = P.ia2 * P.b * P.dt * P.r2d;
-        K.kisg = P.ia2 * P.b * P.dt * P.rd;
+        K.kisg = R(0.25) * P.ia2 * P.b * P.dt * P.rd;   // 1/4: fluxes are carried times four
         K.kf2 = kf * cf[2];
 #pragma unroll
         for (int c = 0; c < V; ++c) {
@@ -137,7 +224,7 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
             all_out = all_out && om[c];
         }
     }
-    const size_t tbase = (size_t)t * m * m + col0;
+    const unsigned tbase = (unsigned)t * m * m + col0;   // shards are < 2^31 elements (checked at create)
     using IO = VecIO<R, V>;
 
     // ---- prologue: rows J0-2 .. J0+1 --------------------------------------------------------
@@ -145,34 +232,38 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     R hc[V], hp[V], nh[V], uc[V], vc[V], nu[V], nv[V], nt[V];
     R c1m[V], Bnm[V], Gs[V], syc[V];
     RowDerived<R, V> Dc;
+    R Yc = yt[J0], ayc = ayt[J0];                         // tan(beta) and 1/(1+Y^2) of the current row
+    R Yn = yt[J0 + 1], ayn = ayt[J0 + 1];                 // ... and of the next one (loaded a row ahead)
+    const int pf_rows = G.prefetch;                       // L2 prefetch distance in rows (0 = off)
+    const bool pf_lane = (lane * (int)(V * sizeof(R))) % 128 == 0;   // one lane per 128-byte line
     {
         R hmm[V], hm1[V], um[V], vm[V], tm[V], tcur[V];
-        IO::ld(P.hq + tbase + (size_t)(J0 - 2) * m, hmm);
-        IO::ld(P.hq + tbase + (size_t)(J0 - 1) * m, hm1);
-        IO::ld(P.hq + tbase + (size_t)J0 * m, hc);
-        IO::ld(P.hq + tbase + (size_t)(J0 + 1) * m, hp);
-        IO::ld(P.uq + tbase + (size_t)(J0 - 1) * m, um);
-        IO::ld(P.vq + tbase + (size_t)(J0 - 1) * m, vm);
-        IO::ld(P.uq + tbase + (size_t)J0 * m, uc);
-        IO::ld(P.vq + tbase + (size_t)J0 * m, vc);
+        IO::ld(P.hq + tbase + (unsigned)(J0 - 2) * m, hmm);
+        IO::ld(P.hq + tbase + (unsigned)(J0 - 1) * m, hm1);
+        IO::ld(P.hq + tbase + (unsigned)J0 * m, hc);
+        IO::ld(P.hq + tbase + (unsigned)(J0 + 1) * m, hp);
+        IO::ld(P.uq + tbase + (unsigned)(J0 - 1) * m, um);
+        IO::ld(P.vq + tbase + (unsigned)(J0 - 1) * m, vm);
+        IO::ld(P.uq + tbase + (unsigned)J0 * m, uc);
+        IO::ld(P.vq + tbase + (unsigned)J0 * m, vc);
 #pragma unroll
         for (int c = 0; c < V; ++c) tm[c] = tcur[c] = nt[c] = R(0);
         if (has_topo) {
-            IO::ld(P.topo + tbase + (size_t)(J0 - 1) * m, tm);
-            IO::ld(P.topo + tbase + (size_t)J0 * m, tcur);
-            IO::ld(P.topo + tbase + (size_t)(J0 + 1) * m, nt);
+            IO::ld(P.topo + tbase + (unsigned)(J0 - 1) * m, tm);
+            IO::ld(P.topo + tbase + (unsigned)J0 * m, tcur);
+            IO::ld(P.topo + tbase + (unsigned)(J0 + 1) * m, nt);
         }
-        IO::ld(P.hq + tbase + (size_t)min(J0 + 2, m - 1) * m, nh);
-        IO::ld(P.uq + tbase + (size_t)(J0 + 1) * m, nu);
-        IO::ld(P.vq + tbase + (size_t)(J0 + 1) * m, nv);
+        IO::ld(P.hq + tbase + (unsigned)min(J0 + 2, m - 1) * m, nh);
+        IO::ld(P.uq + tbase + (unsigned)(J0 + 1) * m, nu);
+        IO::ld(P.vq + tbase + (unsigned)(J0 + 1) * m, nv);
         RowDerived<R, V> Dm;
         march_derive<R, V>(P, K, yt[J0 - 1], ayt[J0 - 1], hm1, um, vm, tm, Dm);
-        march_derive<R, V>(P, K, yt[J0], ayt[J0], hc, uc, vc, tcur, Dc);
+        march_derive<R, V>(P, K, Yc, ayc, hc, uc, vc, tcur, Dc);
 #pragma unroll
         for (int c = 0; c < V; ++c) {
-            const R sym = cs_slope<R, LIM>(hm1[c] - hmm[c], hc[c] - hm1[c]);
-            syc[c] = cs_slope<R, LIM>(hc[c] - hm1[c], hp[c] - hc[c]);
-            Gs[c] = cs_face_flux<R>(Dm.m2[c], Dc.m2[c], hm1[c], sym, hc[c], syc[c]);
+            const R sym = march_half_slope<R, LIM>(hm1[c] - hmm[c], hc[c] - hm1[c]);
+            syc[c] = march_half_slope<R, LIM>(hc[c] - hm1[c], hp[c] - hc[c]);
+            Gs[c] = march_flux4<R>(Dm.m2[c], Dc.m2[c], hm1[c], sym, hc[c], syc[c]);
             c1m[c] = Dm.c1[c];
             Bnm[c] = Dm.Bn[c];
         }
@@ -184,9 +275,9 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     auto row = [&](RowDerived<R, V>& Dcur, RowDerived<R, V>& Dnext, const int J) {
         // loads for the next call (rows J+3 / J+2) and the point-wise q0 of this row
         R ph[V], pu[V], pv[V], pt[V], q0h[V], q0u[V], q0v[V];
-        const size_t oJ = tbase + (size_t)J * m;
-        const size_t o2 = tbase + (size_t)min(J + 2, m - 1) * m;
-        IO::ld(P.hq + tbase + (size_t)min(J + 3, m - 1) * m, ph);
+        const unsigned oJ = tbase + (unsigned)J * m;
+        const unsigned o2 = tbase + (unsigned)min(J + 2, m - 1) * m;
+        IO::ld(P.hq + tbase + (unsigned)min(J + 3, m - 1) * m, ph);
         IO::ld(P.uq + o2, pu);
         IO::ld(P.vq + o2, pv);
         if (has_topo) IO::ld(P.topo + o2, pt);
@@ -195,68 +286,37 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
             IO::ld(P.u0 + oJ, q0u);
             IO::ld(P.v0 + oJ, q0v);
         }
+        // Pull the lines that will be loaded pf_rows rows from now into L2 (no registers involved): the
+        // register prefetch above is one row deep, which covers an L2 hit but not a trip to HBM.
+        if (pf_rows > 0 && pf_lane) {
+            const unsigned op = tbase + (unsigned)min(J + 3 + pf_rows, m - 1) * m;
+            march_prefetch_l2(P.hq + op);
+            march_prefetch_l2(P.uq + op);
+            march_prefetch_l2(P.vq + op);
+            if (has_topo) march_prefetch_l2(P.topo + op);
+            if (read_q0) {
+                const unsigned oq = tbase + (unsigned)min(J + pf_rows, m - 1) * m;
+                march_prefetch_l2(P.h0 + oq);
+                march_prefetch_l2(P.u0 + oq);
+                march_prefetch_l2(P.v0 + oq);
+            }
+        }
 
         // row J+1: derived quantities, y-slope and the north-face flux of row J
-        march_derive<R, V>(P, K, yt[J + 1], ayt[J + 1], hp, nu, nv, nt, Dnext);
+        const R Yn2 = yt[min(J + 2, m - 1)], ayn2 = ayt[min(J + 2, m - 1)];
+        march_derive<R, V>(P, K, Yn, ayn, hp, nu, nv, nt, Dnext);
         R dG[V];
 #pragma unroll
         for (int c = 0; c < V; ++c) {
-            const R syp = cs_slope<R, LIM>(hp[c] - hc[c], nh[c] - hp[c]);
-            const R Gn = cs_face_flux<R>(Dcur.m2[c], Dnext.m2[c], hc[c], syc[c], hp[c], syp);
+            const R syp = march_half_slope<R, LIM>(hp[c] - hc[c], nh[c] - hp[c]);
+            const R Gn = march_flux4<R>(Dcur.m2[c], Dnext.m2[c], hc[c], syc[c], hp[c], syp);
             dG[c] = Gn - Gs[c];
             Gs[c] = Gn;
             syc[c] = syp;
         }
 
-        // row J: x-neighbours from the adjacent lanes
-        R he[V + 4], m1e[V + 2], c2e[V + 2], Bne[V + 2];
-        he[0] = __shfl_up_sync(0xffffffffu, hc[V - 2], 1);
-        he[1] = __shfl_up_sync(0xffffffffu, hc[V - 1], 1);
-        he[V + 2] = __shfl_down_sync(0xffffffffu, hc[0], 1);
-        he[V + 3] = __shfl_down_sync(0xffffffffu, hc[1], 1);
-        m1e[0] = __shfl_up_sync(0xffffffffu, Dcur.m1[V - 1], 1);
-        m1e[V + 1] = __shfl_down_sync(0xffffffffu, Dcur.m1[0], 1);
-        c2e[0] = __shfl_up_sync(0xffffffffu, Dcur.c2[V - 1], 1);
-        c2e[V + 1] = __shfl_down_sync(0xffffffffu, Dcur.c2[0], 1);
-        Bne[0] = __shfl_up_sync(0xffffffffu, Dcur.Bn[V - 1], 1);
-        Bne[V + 1] = __shfl_down_sync(0xffffffffu, Dcur.Bn[0], 1);
-#pragma unroll
-        for (int c = 0; c < V; ++c) {
-            he[c + 2] = hc[c];
-            m1e[c + 1] = Dcur.m1[c];
-            c2e[c + 1] = Dcur.c2[c];
-            Bne[c + 1] = Dcur.Bn[c];
-        }
-        R sxe[V + 2], F[V + 1];
-#pragma unroll
-        for (int k = 0; k < V + 2; ++k) sxe[k] = cs_slope<R, LIM>(he[k + 1] - he[k], he[k + 2] - he[k + 1]);
-#pragma unroll
-        for (int k = 0; k < V + 1; ++k) F[k] = cs_face_flux<R>(m1e[k], m1e[k + 1], he[k + 1], sxe[k], he[k + 2], sxe[k + 1]);
-
-        // tendencies and the RK combination for row J
-        const R ay = ayt[J], Yay = yt[J] * ay;
         R oh[V], ou[V], ov[V];
-#pragma unroll
-        for (int c = 0; c < V; ++c) {
-            // every factor b, dt, 1/delta, 1/a^2 is already inside isg, q and fsg (MarchConst)
-            oh[c] = P.b * hc[c] - ((F[c + 1] - F[c]) + dG[c]) * Dcur.isg[c];
-            ou[c] = P.b * uc[c];
-            ov[c] = P.b * vc[c];
-            if (!P.advect_only) {
-                const R eta = ((c2e[c + 2] - c2e[c]) - (Dnext.c1[c] - c1m[c])) + Dcur.fsg[c];
-                const R T1 = eta * vc[c] - (Bne[c + 2] - Bne[c]);
-                const R T2 = -eta * uc[c] - (Dnext.Bn[c] - Bnm[c]);
-                const R gi11 = Dcur.q[c] * K.ax[c], gi22 = Dcur.q[c] * ay;
-                const R gi12 = (Dcur.q[c] * K.Xax[c]) * Yay;
-                ou[c] += gi11 * T1 + gi12 * T2;
-                ov[c] += gi12 * T1 + gi22 * T2;
-            }
-            if (read_q0) {
-                oh[c] += P.a * q0h[c];
-                ou[c] += P.a * q0u[c];
-                ov[c] += P.a * q0v[c];
-            }
-        }
+        march_row_update<R, V, LIM>(P, K, Dcur, Dnext, hc, uc, vc, dG, c1m, Bnm, Yc, ayc, read_q0, q0h, q0u, q0v, oh, ou, ov);
         if (all_out) {
             IO::st(P.ho + oJ, oh);
             IO::st(P.uo + oJ, ou);
@@ -276,6 +336,7 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
             uc[c] = nu[c], vc[c] = nv[c], nu[c] = pu[c], nv[c] = pv[c];
             if (has_topo) nt[c] = pt[c];
         }
+        Yc = Yn, ayc = ayn, Yn = Yn2, ayn = ayn2;
     };
 
     RowDerived<R, V> Dn;

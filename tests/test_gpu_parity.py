@@ -234,3 +234,15 @@ def test_error_behaviour(built_library):
     with pytest.raises(ValueError):                       # qout aliases the stencil input
         ctx.rk_stage((a, b, c), (a, b, c), (a, b, c), 0.0, 1.0, 1.0)
     ctx.close()
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-13), (np.float32, 2e-5)])
+@pytest.mark.parametrize("name,N,p", [("tc5", 48, 1), ("tc2", 124, 1), ("galewsky", 48, 2)])
+def test_tma_ring_kernel_matches_naive(built_library, dtype, tol, name, N, p):
+    """The TMA-fed kernel (cp.async.bulk ring) against the one-thread-per-cell kernel; N = 124 makes the
+    last warp's row segment ragged, p = 2 exercises tile offsets."""
+    a = _run_case(name, N, 6, p=p, dtype=dtype, kernel="naive")
+    b = _run_case(name, N, 6, p=p, dtype=dtype, kernel="tma")
+    for x, y in zip(a["got"], b["got"]):
+        c = slice(2, 2 + N)
+        assert np.linalg.norm(x[:, c, c] - y[:, c, c]) <= tol * np.linalg.norm(y[:, c, c])

@@ -15,7 +15,7 @@ from cubesphere import api  # noqa: E402
 def main():
     N = int(sys.argv[1]) if len(sys.argv) > 1 else 1536
     for dtype, esize in (("f32", 4), ("f64", 8)):
-        for kernel in ("naive", "march"):
+        for kernel in ("march",):
             ctx = api.Context(N, halo=2, dtype=dtype, kernel=kernel)
             gen = torch.Generator(device="cuda").manual_seed(1)
             h = 1000.0 + 10.0 * torch.rand(ctx.shape, device="cuda", dtype=ctx.dtype, generator=gen)
@@ -24,10 +24,14 @@ def main():
             ctx.halo_fill_state(h, u, v)
             out = [ctx.new_field() for _ in range(3)]
             q0 = [x.clone() for x in (h, u, v)]          # distinct arrays: in a real step q0 != qs for stages 2, 3
-            combos = [(0, 0, 0)] if kernel == "naive" else [(v_, r_, o_) for v_ in ((2, 4) if dtype == "f32" else (2,)) for o_ in ((0,) if (dtype == "f32" and v_ == 2) else (2, 3)) for r_ in (16, 32, 64)]
-            for vec, rows, occ in combos:
-                if vec:
-                    os.environ["CS_MARCH_VEC"], os.environ["CS_MARCH_ROWS"], os.environ["CS_MARCH_OCC"] = str(vec), str(rows), str(occ)
+            if kernel == "march":
+                combos = [(v_, r_, o_, pf) for (v_, o_) in (((2, 0), (4, 2)) if dtype == "f32" else ((2, 2), (2, 3))) for r_ in (16, 32, 64) for pf in (0, 2, 4, 8)]
+            else:
+                combos = [(v_, r_, 0, g_) for v_ in ((2, 4) if dtype == "f32" else (1, 2)) for r_ in (16, 32, 64) for g_ in (5, 8)]
+            for vec, rows, occ, ring in combos:
+                if True:
+                    os.environ["CS_MARCH_VEC"], os.environ["CS_MARCH_ROWS"], os.environ["CS_MARCH_OCC"], os.environ["CS_TMA_RING"] = str(vec or 4), str(rows), str(occ), str(ring or 6)
+                    os.environ["CS_MARCH_PREFETCH"] = str(ring)
                 res = []
                 for a, words in ((0.0, 6), (0.75, 9)):
                     for _ in range(2):
@@ -41,7 +45,7 @@ def main():
                     torch.cuda.synchronize()
                     ms = e0.elapsed_time(e1) / 10
                     res.append((ms, words * esize * 6 * N * N / ms / 1e6))
-                print(f"{dtype} {kernel} vec={vec} occ={occ} rows={rows}: stage1 {res[0][0]:.4f} ms {res[0][1]:.0f} GB/s | stage2 {res[1][0]:.4f} ms {res[1][1]:.0f} GB/s", flush=True)
+                print(f"{dtype} {kernel} vec={vec} occ={occ} rows={rows} ring/pf={ring}: stage1 {res[0][0]:.4f} ms {res[0][1]:.0f} GB/s | stage2 {res[1][0]:.4f} ms {res[1][1]:.0f} GB/s", flush=True)
             ctx.close()
 
 
