@@ -326,9 +326,14 @@ def run_ours(args):
         if secondary:
             line["fp64"] = secondary
         print(json.dumps(line), flush=True)
+    sys.stdout.flush()
     if world > 1:
+        # a rank that is slow to tear NCCL down must not hold the job: hard exit after a grace period
+        threading.Timer(60.0, lambda: os._exit(0)).start()
+        stepper.close()
         dist.barrier()
         dist.destroy_process_group()
+        os._exit(0)
 
 
 def main():

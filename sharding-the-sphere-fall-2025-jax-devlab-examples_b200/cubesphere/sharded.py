@@ -31,8 +31,13 @@ RK_PAIRS = {
 class ShardedStepper:
     def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f32", rk="ssprk3", limiter="mc", advect_only=False,
                  axis=(0.0, 0.0, 1.0), device=0, rank=0, world=1, kernel="auto", tangents=None, overlap=True,
-                 group=None):
+                 group=None, use_graph=True):
         self.rank, self.world, self.rk, self.overlap, self.group = rank, world, rk, overlap, group
+        # world > 1: a step is ~30 host calls (kernel launches, stream waits, one NCCL all-to-all per stage);
+        # captured once into a CUDA graph per (dt, state tensors) and replayed, so the host never paces the GPUs
+        self.use_graph = use_graph and world > 1
+        self._graphs = {}
+        self._eager_calls = {}
         self.ranges = block_ranges(topology.num_tiles(tiles_per_edge), world)
         self.tile_begin, self.tile_count = self.ranges[rank]
         self.ctx = api.Context(N, tiles_per_edge=tiles_per_edge, halo=halo, dtype=dtype, rk=rk, limiter=limiter,
@@ -58,6 +63,9 @@ class ShardedStepper:
         return self.ctx.launches + self._extra_launches
 
     def close(self):
+        # graphs hold NCCL work: drop them (and drain the device) before the process group goes away
+        self._graphs.clear()
+        torch.cuda.synchronize(self.device)
         self.ctx.close()
 
     # -- halo -------------------------------------------------------------------------------
@@ -87,6 +95,30 @@ class ShardedStepper:
         if self.world == 1:
             self.ctx.step(h, u, v, dt)
             return h, u, v
+        if not self.use_graph:
+            return self._step_sharded(h, u, v, dt)
+        key = (float(dt), h.data_ptr(), u.data_ptr(), v.data_ptr())
+        graph = self._graphs.get(key)
+        if graph is None:
+            # the first two calls run eagerly (NCCL warm-up, lazy initialisation), the third is captured
+            n = self._eager_calls.get(key, 0)
+            if n < 2:
+                self._eager_calls[key] = n + 1
+                return self._step_sharded(h, u, v, dt)
+            torch.cuda.synchronize(self.device)
+            graph = torch.cuda.CUDAGraph()
+            launches0 = self.ctx.launches
+            with torch.cuda.graph(graph):
+                self._step_sharded(h, u, v, dt)
+            self._graph_launches = self.ctx.launches - launches0     # kernels of ours inside one replay
+            self._graphs[key] = graph
+            self._extra_launches -= self._graph_launches              # counted once by the capture itself
+            # capture does not execute: fall through and replay once so this call does advance the state
+        graph.replay()
+        self._extra_launches += self._graph_launches
+        return h, u, v
+
+    def _step_sharded(self, h, u, v, dt):
         q0 = (h, u, v)
         cur = q0
         pairs = RK_PAIRS[self.rk]

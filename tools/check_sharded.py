@@ -1,0 +1,55 @@
+#!/usr/bin/env python
+"""Multi-GPU parity check (run under torchrun, one rank per GPU): the sharded stepper -- rim / inner
+split, NCCL all-to-all of packed halos overlapped with the inner cells -- against the CPU oracle."""
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT / "sharding-the-sphere-fall-2025-jax-devlab-examples_b200"))
+sys.path.insert(0, str(ROOT))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+from cubesphere import cases, sharded  # noqa: E402
+from oracle import cs_oracle_np as orc  # noqa: E402
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+ok = True
+for N, p, overlap in ((48, 2 if world > 3 else 1, True), (96, 2, True), (96, 2, False)):
+    if (6 * p * p) % world:
+        continue
+    g, steps = 2, 10
+    case = cases.make_case("tc2", N, alpha0=0.6)
+    par = orc.Params(N, g, axis=case.axis)
+    ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
+    st = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis, device=local, rank=rank,
+                                world=world, tangents=orc.centre_tangents(N), overlap=overlap)
+    b, c = st.tile_begin, st.tile_count
+    n = N // p
+    raw = [orc.faces_to_tiles(orc.pad(x, g), p, g)[b:b + c] for x in (case.h, case.u1, case.u2)]   # ghosts empty
+    dev = [torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in raw]
+    st.halo_fill(*dev)
+    dt = cases.stable_dt(case)
+    m0 = st.diagnostics(*dev).cpu().numpy()
+    for _ in range(steps):
+        st.step(*dev, dt)
+        ref = orc.step(par, ref, dt)
+    m1 = st.diagnostics(*dev).cpu().numpy()
+    want = [orc.faces_to_tiles(x, p, g)[b:b + c] for x in ref]
+    errs = []
+    for got, w in zip(dev, want):
+        a = got.cpu().numpy()
+        errs.append(float(np.linalg.norm(a[:, g:g + n, g:g + n] - w[:, g:g + n, g:g + n]) / np.linalg.norm(w[:, g:g + n, g:g + n])))
+        errs.append(float(np.linalg.norm(a[:, g:g + n, :] - w[:, g:g + n, :]) / np.linalg.norm(w[:, g:g + n, :])))
+    mo = orc.diagnostics(par, *ref)
+    good = max(errs) <= 1e-12 and abs(m1[0] - m0[0]) <= 1e-13 * m0[0] and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
+    ok = ok and good
+    print(f"rank {rank}/{world} C{N} p={p} overlap={overlap}: max rel err {max(errs):.2e}, mass drift {(m1[0]-m0[0])/m0[0]:.1e} -> {'ok' if good else 'FAIL'}", flush=True)
+    st.close()
+t = torch.tensor([int(ok)], device="cuda")
+dist.all_reduce(t, op=dist.ReduceOp.MIN)
+dist.destroy_process_group()
+sys.exit(0 if int(t.item()) == 1 else 1)
