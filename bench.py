@@ -65,32 +65,45 @@ def measured_peak_gbs():
 
 
 class ClockSampler:
-    """nvidia-smi SM clock / throttle-reason samples during the timed region."""
+    """nvidia-smi SM clock / throttle-reason samples (one streaming process, 50 ms period) taken while
+    the GPU measurements run: the timed steps, the per-launch stage timing and the end-to-end loop."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index=0):
-        self.index, self.samples, self._stop, self._t = index, [], threading.Event(), None
+        self.index, self.samples, self._proc, self._t = index, [], None, None
 
     def _run(self):
-        while not self._stop.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
-            except Exception:
-                pass
-            self._stop.wait(0.1)
+        for line in self._proc.stdout:
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) >= 6:
+                self.samples.append(parts)
 
-    def __enter__(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
+    def start(self):
+        try:
+            self._proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                           "-i", str(self.index), "-lms", "50"], stdout=subprocess.PIPE, text=True)
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        except Exception:
+            self._proc = None
         return self
 
+    def stop(self):
+        if self._proc is not None:
+            self._proc.terminate()
+            try:
+                self._proc.wait(timeout=5)
+            except Exception:
+                self._proc.kill()
+            self._t.join(timeout=5)
+            self._proc = None
+
+    def __enter__(self):
+        return self.start()
+
     def __exit__(self, *a):
-        self._stop.set()
-        self._t.join(timeout=6)
+        self.stop()
 
     def summary(self):
         mhz, mx, reasons = [], 0.0, set()
@@ -221,12 +234,16 @@ def run_ours(args):
     barrier()
     l0 = stepper.launches
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
-        ev0.record()
-        for _ in range(args.steps):
-            stepper.step(*dev, dt)
-        ev1.record()
-        barrier()
+    clk = ClockSampler(local).start()
+    time.sleep(0.15)                               # let the sampler come up; the GPU is warm from the warm-up steps
+    for _ in range(args.warmup):
+        stepper.step(*dev, dt)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        stepper.step(*dev, dt)
+    ev1.record()
+    barrier()
     ms = ev0.elapsed_time(ev1)
     launches = stepper.launches - l0
     if world > 1:
@@ -274,6 +291,8 @@ def run_ours(args):
                               "d2h_bytes_per_step": nbytes + 16, "ms_per_step": ms_b}}
     else:
         e2e = stepper.time_e2e(pinned, dev, dt, max(3, min(args.steps, 5)), cells_total)
+
+    clk.stop()
 
     # ---- fp64 side measurement (the metric is quoted for fp64 and fp32) ------------------------
     secondary = None

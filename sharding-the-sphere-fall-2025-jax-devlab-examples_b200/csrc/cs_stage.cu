@@ -5,6 +5,8 @@
 #include "cs_stage_tma.cuh"
 
 #include <cstdlib>
+#include <map>
+#include <utility>
 
 namespace {
 
@@ -102,29 +104,55 @@ int launch_rim(cs_ctx* ctx, const StageParams<R>& P, cudaStream_t s) {
     return CS_OK;
 }
 
-// Strip height: tall strips amortise the 4-row prologue, short ones keep enough warps in flight
-// on small grids.  Tuned on C1536 (profiles/r01_stage_sweep_*.log); CS_MARCH_ROWS overrides.
-int default_rows(int n, int T, bool f32) {
-    const long long cells = (long long)n * n * T;
-    if (cells >= 8000000) return f32 ? 64 : 32;
-    if (cells >= 500000) return 32;
-    return 16;
+// Work decomposition shared by the marching kernels: one warp per (tile, strip, chunk).
+// Strip height trades the 4-row prologue of every strip against whole "waves" of warps: with W warp
+// slots on the GPU the launch takes ceil(items / W) rounds of (rows + prologue) row-times, so the
+// height is chosen to minimise that product (CS_MARCH_ROWS overrides).
+template <typename Kernel>
+MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m, int T, int lo, int hi, size_t smem) {
+    MarchGeom G;
+    G.xlo = G.ylo = lo, G.xhi = G.yhi = hi;
+    G.prefetch = env_int("CS_MARCH_PREFETCH", 2);
+    G.ngroups = m / V;
+    G.grp0 = (lo + g) / V;
+    const int grp_last = (hi - 1 + g) / V;
+    G.nchunks = (grp_last - G.grp0 + 1 + CS_MARCH_OUT_LANES - 1) / CS_MARCH_OUT_LANES;
+    static std::map<std::pair<const void*, size_t>, int> occupancy;      // per kernel instantiation and smem size
+    const auto key = std::make_pair(reinterpret_cast<const void*>(kernel), smem);
+    auto it = occupancy.find(key);
+    if (it == occupancy.end()) {
+        int bps = 1;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kernel, CS_MARCH_THREADS, smem) != cudaSuccess || bps < 1) {
+            cudaGetLastError();
+            bps = 1;
+        }
+        it = occupancy.emplace(key, bps).first;
+    }
+    const int blocks_per_sm = it->second;
+    const long long slots = (long long)ctx->num_sms * blocks_per_sm * (CS_MARCH_THREADS / 32);
+    const int span = hi - lo;
+    int best_rows = span < 8 ? span : 8;
+    double best_cost = 1e300;
+    for (int rows = 8; rows <= 256 && rows <= span + 7; rows += 4) {
+        const int r = rows < span ? rows : span;
+        const long long items = (long long)G.nchunks * ((span + r - 1) / r) * T;
+        const long long waves = (items + slots - 1) / slots;
+        const double cost = (double)waves * (r + 5);
+        if (cost < best_cost) best_cost = cost, best_rows = r;
+    }
+    G.rows = env_int("CS_MARCH_ROWS", best_rows);
+    if (G.rows < 1) G.rows = 1;
+    G.nstrips = (span + G.rows - 1) / G.rows;
+    G.nitems = G.nchunks * G.nstrips * T;
+    (void)n;
+    return G;
 }
 
 template <typename R, int V, int LIM, int MINB>
 int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_t s) {
-    MarchGeom G;
-    G.xlo = G.ylo = lo, G.xhi = G.yhi = hi;
-    G.rows = env_int("CS_MARCH_ROWS", default_rows(P.n, P.T, sizeof(R) == 4));
-    G.prefetch = env_int("CS_MARCH_PREFETCH", 2);
-    if (G.rows < 1) G.rows = 1;
-    G.ngroups = P.m / V;
-    G.grp0 = (lo + P.g) / V;
-    const int grp_last = (hi - 1 + P.g) / V;
-    G.nchunks = (grp_last - G.grp0 + 1 + CS_MARCH_OUT_LANES - 1) / CS_MARCH_OUT_LANES;
+    const MarchGeom G = march_geometry(ctx, stage_march_kernel<R, V, LIM, MINB>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
     const int warps = CS_MARCH_THREADS / 32;
-    dim3 grid((G.nchunks + warps - 1) / warps, (hi - lo + G.rows - 1) / G.rows, P.T);
-    stage_march_kernel<R, V, LIM, MINB><<<grid, CS_MARCH_THREADS, 0, s>>>(P, G);
+    stage_march_kernel<R, V, LIM, MINB><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, 0, s>>>(P, G);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;
@@ -132,15 +160,6 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStrea
 
 template <typename R, int V, int LIM, int MINB>
 int launch_tma(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_t s) {
-    MarchGeom G;
-    G.xlo = G.ylo = lo, G.xhi = G.yhi = hi;
-    G.rows = env_int("CS_MARCH_ROWS", 32);
-    G.prefetch = env_int("CS_MARCH_PREFETCH", 4);
-    if (G.rows < 1) G.rows = 1;
-    G.ngroups = P.m / V;
-    G.grp0 = (lo + P.g) / V;
-    const int grp_last = (hi - 1 + P.g) / V;
-    G.nchunks = (grp_last - G.grp0 + 1 + CS_MARCH_OUT_LANES - 1) / CS_MARCH_OUT_LANES;
     const int warps = CS_MARCH_THREADS / 32;
     int ring = env_int("CS_TMA_RING", 6);
     ring = ring < 4 ? 4 : ring > CS_TMA_MAX_RING ? CS_TMA_MAX_RING : ring;
@@ -151,8 +170,8 @@ int launch_tma(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_
         CS_CUDA(ctx, cudaFuncSetAttribute(stage_tma_kernel<R, V, LIM, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    dim3 grid((G.nchunks + warps - 1) / warps, (hi - lo + G.rows - 1) / G.rows, P.T);
-    stage_tma_kernel<R, V, LIM, MINB><<<grid, CS_MARCH_THREADS, smem, s>>>(P, G, ring);
+    const MarchGeom G = march_geometry(ctx, stage_tma_kernel<R, V, LIM, MINB>, V, P.n, P.g, P.m, P.T, lo, hi, smem);
+    stage_tma_kernel<R, V, LIM, MINB><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, smem, s>>>(P, G, ring);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;

@@ -22,6 +22,8 @@ struct MarchGeom {
     int grp0;                 // first column group that contains an output column
     int ngroups;              // column groups per row (m / V)
     int nchunks;              // warps along x
+    int nstrips;              // strips along y
+    int nitems;               // nchunks * nstrips * tiles (one warp each)
 };
 
 __device__ __forceinline__ void march_prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -189,10 +191,14 @@ template <typename R, int V, int LIM, int MINB>
 __global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
 stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant__ MarchGeom G) {
     const int lane = threadIdx.x & 31;
-    const int chunk = blockIdx.x * (CS_MARCH_THREADS / 32) + (threadIdx.x >> 5);
-    if (chunk >= G.nchunks) return;                       // whole warp leaves together
-    const int t = blockIdx.z;
-    const int j0 = G.ylo + blockIdx.y * G.rows;
+    // work items are (tile, strip, chunk) triples, chunk fastest, one per warp: consecutive warps take
+    // neighbouring column chunks of the same strip, and no warp slot idles when nchunks % 4 != 0
+    const int item = blockIdx.x * (CS_MARCH_THREADS / 32) + (threadIdx.x >> 5);
+    if (item >= G.nitems) return;                         // whole warp leaves together
+    const int chunk = item % G.nchunks;
+    const int strip = (item / G.nchunks) % G.nstrips;
+    const int t = item / (G.nchunks * G.nstrips);
+    const int j0 = G.ylo + strip * G.rows;
     const int j1 = min(j0 + G.rows, G.yhi);
     const int m = P.m, g = P.g;
     const TileCoord tc = cs_tile_coord(t + P.t0, P.p);

@@ -93,10 +93,12 @@ stage_tma_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant
     constexpr uint32_t AS = cs_tma_astride<R, V>();
     extern __shared__ __align__(128) unsigned char cs_tma_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int chunk = blockIdx.x * (CS_MARCH_THREADS / 32) + warp;
-    if (chunk >= G.nchunks) return;                       // whole warp leaves together
-    const int t = blockIdx.z;
-    const int j0 = G.ylo + blockIdx.y * G.rows;
+    const int item = blockIdx.x * (CS_MARCH_THREADS / 32) + warp;      // (tile, strip, chunk), chunk fastest
+    if (item >= G.nitems) return;                         // whole warp leaves together
+    const int chunk = item % G.nchunks;
+    const int strip = (item / G.nchunks) % G.nstrips;
+    const int t = item / (G.nchunks * G.nstrips);
+    const int j0 = G.ylo + strip * G.rows;
     const int j1 = min(j0 + G.rows, G.yhi);
     const int m = P.m, g = P.g;
     const TileCoord tc = cs_tile_coord(t + P.t0, P.p);

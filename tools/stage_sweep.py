@@ -25,12 +25,16 @@ def main():
             out = [ctx.new_field() for _ in range(3)]
             q0 = [x.clone() for x in (h, u, v)]          # distinct arrays: in a real step q0 != qs for stages 2, 3
             if kernel == "march":
-                combos = [(v_, r_, o_, pf) for (v_, o_) in (((2, 0), (4, 2)) if dtype == "f32" else ((2, 2), (2, 3))) for r_ in (16, 32, 64) for pf in (0, 2, 4, 8)]
+                combos = [(v_, r_, o_, pf) for (v_, o_) in (((4, 2),) if dtype == "f32" else ((2, 2),)) for r_ in ((0, 64, 104, 128) if dtype == "f32" else (0, 32, 48, 52, 64)) for pf in (2,)]
             else:
                 combos = [(v_, r_, 0, g_) for v_ in ((2, 4) if dtype == "f32" else (1, 2)) for r_ in (16, 32, 64) for g_ in (5, 8)]
             for vec, rows, occ, ring in combos:
                 if True:
-                    os.environ["CS_MARCH_VEC"], os.environ["CS_MARCH_ROWS"], os.environ["CS_MARCH_OCC"], os.environ["CS_TMA_RING"] = str(vec or 4), str(rows), str(occ), str(ring or 6)
+                    os.environ["CS_MARCH_VEC"], os.environ["CS_MARCH_OCC"], os.environ["CS_TMA_RING"] = str(vec or 4), str(occ), str(ring or 6)
+                    if rows:
+                        os.environ["CS_MARCH_ROWS"] = str(rows)
+                    else:
+                        os.environ.pop("CS_MARCH_ROWS", None)
                     os.environ["CS_MARCH_PREFETCH"] = str(ring)
                 res = []
                 for a, words in ((0.0, 6), (0.75, 9)):
