@@ -232,13 +232,13 @@ def run_ours(args):
     for _ in range(args.warmup):
         stepper.step(*dev, dt)
     barrier()
-    l0 = stepper.launches
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     clk = ClockSampler(local).start()
     time.sleep(0.15)                               # let the sampler come up; the GPU is warm from the warm-up steps
     for _ in range(args.warmup):
         stepper.step(*dev, dt)
     barrier()
+    l0 = stepper.launches
     ev0.record()
     for _ in range(args.steps):
         stepper.step(*dev, dt)
@@ -259,10 +259,37 @@ def run_ours(args):
     words = {True: 6, False: 9}                    # stage 1 reads qs, writes out; later stages also read q0
     alg_bytes = sum(words[a == 0.0] for a in roof["a"]) * esize * cells_local
     achieved = alg_bytes / (sum(roof["ms"]) * 1e-3) / 1e9
+    # traffic: dram__bytes_read + dram__bytes_write per launch from the committed `ncu --set full` capture of
+    # this kernel (profiles/r01_traffic.json); only quoted when the capture's configuration is the one running
+    traffic = None
+    try:
+        tr = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())
+        key = f"{args.dtype}_C{N}_tiles{tc}"
+        if key in tr:
+            traffic = tr[key]["dram_bytes_per_launch"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_kind": peak_kind, "kernel": roof["kernel"],
+                "traffic": traffic, "peak_kind": peak_kind, "kernel": roof["kernel"],
+                "algorithmic_bytes_per_launch": alg_bytes / len(roof["ms"]),
                 "algorithmic_bytes_per_cell_step": 24 * esize,
-                "stage_ms": [float(x) for x in roof["ms"]], "frac_of_nominal_8TBs": achieved / 8000.0}
+                "stage_ms": [float(x) for x in roof["ms"]], "frac_of_nominal_8TBs": achieved / 8000.0,
+                "whole_step_frac": 24 * esize * cells_total / world / (ms / args.steps * 1e-3) / 1e9 / peak}
+
+    # ---- halo: the ghost-fill launch alone, and what the step pays beyond its three stage kernels -------
+    halo = None
+    if world == 1:
+        hev0, hev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(5):
+            stepper.ctx.halo_fill_state(*dev)
+        hev0.record()
+        for _ in range(100):
+            stepper.ctx.halo_fill_state(*dev)
+        hev1.record()
+        torch.cuda.synchronize()
+        fill_us = hev0.elapsed_time(hev1) * 1e3 / 100
+        halo = {"fill_us": fill_us, "fills_per_step": len(roof["ms"]), "halo_us_per_step": fill_us * len(roof["ms"]),
+                "exposed_us_per_step": max(0.0, (ms / args.steps - sum(roof["ms"])) * 1e3)}
 
     # ---- end to end through the host-buffer entry point ---------------------------------------
     e2e = None
@@ -339,7 +366,7 @@ def run_ours(args):
                        "l2": "state (3 x %.0f MB x 3 buffers per GPU) is larger than L2; no flush needed" %
                              (cells_local * esize / 1e6),
                        "finite": finite},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "halo": halo, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clk.summary(),
         }
         if secondary:
