@@ -190,7 +190,7 @@ def run_reference(args):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from cubesphere import api, sharded
+    from cubesphere import api, partition, sharded
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -209,16 +209,31 @@ def run_ours(args):
     tdtype = torch.float32 if args.dtype == "f32" else torch.float64
     ndtype = np.float32 if args.dtype == "f32" else np.float64
     esize = 4 if args.dtype == "f32" else 8
-    case, dt = initial_state(args.case, N)
+    ranges = partition.block_ranges(6 * p * p, world)
+    t0, tc = ranges[rank]
+    # every rank builds only its own tiles of the initial condition (interior cells [tc, n, n])
+    from cubesphere import cases
+    case = cases.make_case(args.case, N, p=p, tiles=range(t0, t0 + tc))
+    dt = cases.stable_dt(case, 0.5)
+    if world > 1:
+        tdt = torch.tensor([dt], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tdt, op=dist.ReduceOp.MIN)
+        dt = float(tdt.item())
     stepper = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
                                      advect_only=case.advect_only, device=local, rank=rank, world=world,
                                      kernel=args.kernel)
-    t0, tc = stepper.tile_begin, stepper.tile_count
-    host = [faces_to_padded_tiles(x, p, g, ndtype)[t0:t0 + tc] for x in (case.h, case.u1, case.u2)]
+    assert (stepper.tile_begin, stepper.tile_count) == (t0, tc)
+
+    def padded(field):
+        out = np.zeros((field.shape[0], field.shape[1] + 2 * g, field.shape[2] + 2 * g), dtype=ndtype)
+        out[:, g:-g, g:-g] = field
+        return out
+
+    host = [padded(x) for x in (case.h, case.u1, case.u2)]
     pinned = [torch.from_numpy(x).pin_memory() for x in host]
     dev = [x.cuda(non_blocking=True) for x in pinned]
     if case.hs is not None:
-        stepper.set_topography(torch.from_numpy(faces_to_padded_tiles(case.hs, p, g, ndtype)[t0:t0 + tc]).cuda())
+        stepper.set_topography(torch.from_numpy(padded(case.hs)).cuda())
     stepper.halo_fill(*dev)
     cells_total = 6.0 * N * N
     cells_local = float(tc) * stepper.n * stepper.n

@@ -39,18 +39,19 @@ def _solid_body_wind(lon, lat, u0, alpha0):
     return u, v
 
 
-def _to_panel(u_east, v_north, pts, N, a):
+def _to_panel(u_east, v_north, pts, patch, a):
     V = geo.cartesian_from_lonlat_wind(u_east, v_north, pts)
-    return geo.contravariant_from_cartesian(V, N, a)
+    return geo.contravariant_from_cartesian(V, patch.N, a, patch=patch)
 
 
-def tc1(N, alpha0=0.0, a=geo.EARTH_RADIUS):
+def tc1(N, alpha0=0.0, a=geo.EARTH_RADIUS, p=1, tiles=None):
     """Cosine-bell advection by solid-body rotation (velocity frozen)."""
-    pts = geo.face_points(N)
+    patch = geo.Patch(N, p, tiles)
+    pts = patch.points()
     lon, lat = geo.lonlat(pts)
     u0 = 2.0 * np.pi * a / (12.0 * DAY)
     ue, vn = _solid_body_wind(lon, lat, u0, alpha0)
-    u1, u2 = _to_panel(ue, vn, pts, N, a)
+    u1, u2 = _to_panel(ue, vn, pts, patch, a)
     lon_c, lat_c, h0, R = 1.5 * np.pi, 0.0, 1000.0, a / 3.0
     cosd = np.sin(lat_c) * np.sin(lat) + np.cos(lat_c) * np.cos(lat) * np.cos(lon - lon_c)
     r = a * np.arccos(np.clip(cosd, -1.0, 1.0))
@@ -64,25 +65,27 @@ def _geostrophic_height(lon, lat, gh0, u0, alpha0, a, omega, grav):
     return (gh0 - (a * omega * u0 + 0.5 * u0 * u0) * s * s) / grav
 
 
-def tc2(N, alpha0=0.0, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY):
+def tc2(N, alpha0=0.0, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY, p=1, tiles=None):
     """Steady zonal geostrophic flow; the initial condition is the exact solution."""
-    pts = geo.face_points(N)
+    patch = geo.Patch(N, p, tiles)
+    pts = patch.points()
     lon, lat = geo.lonlat(pts)
     u0 = 2.0 * np.pi * a / (12.0 * DAY)
     ue, vn = _solid_body_wind(lon, lat, u0, alpha0)
-    u1, u2 = _to_panel(ue, vn, pts, N, a)
+    u1, u2 = _to_panel(ue, vn, pts, patch, a)
     h = _geostrophic_height(lon, lat, 2.94e4, u0, alpha0, a, omega, grav)
     return Case("tc2", N, h, u1, u2, None, (-np.sin(alpha0), 0.0, np.cos(alpha0)), False,
                 dict(u0=u0, alpha0=alpha0))
 
 
-def tc5(N, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY):
+def tc5(N, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY, p=1, tiles=None):
     """Zonal flow over an isolated conical mountain."""
-    pts = geo.face_points(N)
+    patch = geo.Patch(N, p, tiles)
+    pts = patch.points()
     lon, lat = geo.lonlat(pts)
     u0, h0 = 20.0, 5960.0
     ue, vn = _solid_body_wind(lon, lat, u0, 0.0)
-    u1, u2 = _to_panel(ue, vn, pts, N, a)
+    u1, u2 = _to_panel(ue, vn, pts, patch, a)
     total = _geostrophic_height(lon, lat, grav * h0, u0, 0.0, a, omega, grav)
     R, lon_c, lat_c = np.pi / 9.0, 1.5 * np.pi, np.pi / 6.0
     r = np.sqrt(np.minimum(R * R, (lon - lon_c) ** 2 + (lat - lat_c) ** 2))
@@ -90,9 +93,10 @@ def tc5(N, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY):
     return Case("tc5", N, total - hs, u1, u2, hs, (0.0, 0.0, 1.0), False, dict(u0=u0))
 
 
-def tc6(N, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY):
+def tc6(N, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY, p=1, tiles=None):
     """Rossby-Haurwitz wave, wavenumber 4."""
-    pts = geo.face_points(N)
+    patch = geo.Patch(N, p, tiles)
+    pts = patch.points()
     lon, lat = geo.lonlat(pts)
     w = K = 7.848e-6
     R, h0 = 4.0, 8000.0
@@ -105,13 +109,14 @@ def tc6(N, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY):
     B = 2 * (omega + w) * K / ((R + 1) * (R + 2)) * c ** R * ((R * R + 2 * R + 2) - (R + 1) ** 2 * c * c)
     C = 0.25 * K * K * c ** (2 * R) * ((R + 1) * c * c - (R + 2))
     h = h0 + (a * a / grav) * (A + B * np.cos(R * lon) + C * np.cos(2 * R * lon))
-    u1, u2 = _to_panel(ue, vn, pts, N, a)
+    u1, u2 = _to_panel(ue, vn, pts, patch, a)
     return Case("tc6", N, h, u1, u2, None, (0.0, 0.0, 1.0), False, {})
 
 
-def galewsky(N, perturbed=True, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY):
+def galewsky(N, perturbed=True, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=geo.EARTH_GRAVITY, p=1, tiles=None):
     """Barotropically unstable mid-latitude jet (Galewsky, Scott & Polvani 2004)."""
-    pts = geo.face_points(N)
+    patch = geo.Patch(N, p, tiles)
+    pts = patch.points()
     lon, lat = geo.lonlat(pts)
     umax, phi0 = 80.0, np.pi / 7.0
     phi1 = 0.5 * np.pi - phi0
@@ -135,7 +140,7 @@ def galewsky(N, perturbed=True, a=geo.EARTH_RADIUS, omega=geo.EARTH_OMEGA, grav=
     if perturbed:
         lam = np.where(lon > np.pi, lon - 2.0 * np.pi, lon)
         h = h + 120.0 * np.cos(lat) * np.exp(-(lam * 3.0) ** 2) * np.exp(-((np.pi / 4.0 - lat) * 15.0) ** 2)
-    u1, u2 = _to_panel(jet(lat), np.zeros_like(lat), pts, N, a)
+    u1, u2 = _to_panel(jet(lat), np.zeros_like(lat), pts, patch, a)
     return Case("galewsky", N, h, u1, u2, None, (0.0, 0.0, 1.0), False, {})
 
 
@@ -147,15 +152,16 @@ def make_case(name: str, N: int, **kw) -> Case:
         fn = CASES[name]
     except KeyError:
         raise ValueError(f"Unknown case: {name}; choose from {sorted(CASES)}") from None
-    return fn(N, **kw)
+    case = fn(N, **kw)
+    case.meta["patch"] = geo.Patch(N, kw.get("p", 1), kw.get("tiles"))
+    return case
 
 
 def stable_dt(case: Case, cfl=0.5, a=geo.EARTH_RADIUS, grav=geo.EARTH_GRAVITY):
     """Time step from the advective + gravity-wave CFL number in (alpha, beta) space."""
     N = case.N
-    t = geo.centre_tangents(N)
-    X, Y = np.meshgrid(t, t, indexing="xy")
-    m = geo.metric_terms(X, Y, a)
+    patch = case.meta.get("patch") or geo.Patch(N)
+    m = geo.metric_terms(patch.X, patch.Y, a)
     c = 0.0 if case.advect_only else np.sqrt(grav * np.maximum(case.h + (0 if case.hs is None else 0), 0.0))
     s1 = np.abs(case.u1) + c * np.sqrt(m["gi11"])
     s2 = np.abs(case.u2) + c * np.sqrt(m["gi22"])

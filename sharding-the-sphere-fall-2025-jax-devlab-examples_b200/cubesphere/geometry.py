@@ -87,6 +87,50 @@ def face_points(N: int, g: int = 0):
     return out
 
 
+class Patch:
+    """Cell-centre coordinates of a set of tiles: faces [K], X, Y [K, n, n] (X along axis 2, Y along axis 1).
+
+    ``tiles=None`` means all 6 p^2 tiles in order; with p = 1 that is the six whole faces.  Initial
+    conditions are evaluated patch by patch so that a rank only ever builds its own shard.
+    """
+
+    def __init__(self, N, p=1, tiles=None):
+        if N % p:
+            raise ValueError(f"N = {N} is not divisible by tiles_per_edge = {p}")
+        n = N // p
+        t = centre_tangents(N)
+        tiles = list(range(6 * p * p)) if tiles is None else list(tiles)
+        self.N, self.p, self.n, self.tiles = N, p, n, tiles
+        self.faces = np.empty(len(tiles), dtype=np.int64)
+        self.X = np.empty((len(tiles), n, n))
+        self.Y = np.empty((len(tiles), n, n))
+        for k, tile in enumerate(tiles):
+            f, r = divmod(tile, p * p)
+            ty, tx = divmod(r, p)
+            self.faces[k] = f
+            self.X[k], self.Y[k] = np.meshgrid(t[tx * n:(tx + 1) * n], t[ty * n:(ty + 1) * n], indexing="xy")
+
+    def _frames(self):
+        fr = np.asarray(FACE_FRAMES, dtype=np.float64)[self.faces]          # [K, 3(normal, x, y), 3]
+        return fr[:, 0, None, None, :], fr[:, 1, None, None, :], fr[:, 2, None, None, :]
+
+    def points(self):
+        """Unit position vectors [K, n, n, 3]."""
+        nrm, ex, ey = self._frames()
+        r = nrm + self.X[..., None] * ex + self.Y[..., None] * ey
+        return r / np.linalg.norm(r, axis=-1, keepdims=True)
+
+    def basis(self, a=EARTH_RADIUS):
+        """d r / d alpha, d r / d beta at the cell centres: two arrays [K, n, n, 3]."""
+        nrm, ex, ey = self._frames()
+        X, Y = self.X, self.Y
+        rho = np.sqrt(1.0 + X * X + Y * Y)
+        P = nrm + X[..., None] * ex + Y[..., None] * ey
+        e_a = a * (1.0 + X * X)[..., None] * (ex / rho[..., None] - P * (X / rho ** 3)[..., None])
+        e_b = a * (1.0 + Y * Y)[..., None] * (ey / rho[..., None] - P * (Y / rho ** 3)[..., None])
+        return e_a, e_b
+
+
 def lonlat(points):
     """Longitude in [0, 2 pi) and latitude from unit vectors [..., 3]."""
     lon = np.mod(np.arctan2(points[..., 1], points[..., 0]), 2.0 * np.pi)
@@ -109,9 +153,9 @@ def tangent_basis(N: int, a=EARTH_RADIUS):
     return e_a, e_b
 
 
-def contravariant_from_cartesian(V, N: int, a=EARTH_RADIUS):
-    """Panel-local contravariant components (rad/s) of Cartesian velocities V [6, N, N, 3] (m/s)."""
-    e_a, e_b = tangent_basis(N, a)
+def contravariant_from_cartesian(V, N: int, a=EARTH_RADIUS, patch=None):
+    """Panel-local contravariant components (rad/s) of Cartesian velocities V [K, n, n, 3] (m/s)."""
+    e_a, e_b = tangent_basis(N, a) if patch is None else patch.basis(a)
     g11 = np.sum(e_a * e_a, -1)
     g12 = np.sum(e_a * e_b, -1)
     g22 = np.sum(e_b * e_b, -1)
