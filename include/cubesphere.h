@@ -84,7 +84,9 @@ typedef struct cs_config {
     int32_t tile_begin;       /* first tile owned by this context                            */
     int32_t tile_count;       /* number of tiles owned; 0 = all 6 p^2                        */
     int32_t kernel;           /* CS_KERNEL_*                                                 */
-    int32_t fused_halo;       /* 1: stage kernel stores boundary cells into neighbour ghosts */
+    int32_t fused_halo;       /* 1: stage kernel also stores boundary cells into the neighbours' edge ghosts  */
+                              /*    (no halo launch; corner blocks not refreshed).  Off by default: measured  */
+                              /*    slower than the separate 3-microsecond halo launch   */
     int32_t reserved[3];
     double radius;            /* a      (0 -> 6.37122e6 m)                                   */
     double omega;             /* Omega  (0 -> 7.292e-5 1/s; set advect_only for no rotation) */

@@ -62,7 +62,7 @@ extern "C" int cs_rk_stage(cs_ctx* ctx, const void* const q0[3], const void* con
     int rc = cs_rk_stage_part(ctx, q0, qs, qout, a, b, dt, 2, stream);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    if ((rc = cs_launch_halo(ctx, qout[0], qout[1], qout[2], 3, s))) return rc;
+    if (!ctx->stage_pushed && (rc = cs_launch_halo(ctx, qout[0], qout[1], qout[2], 3, s))) return rc;
     if (diag_out) return cs_launch_diag(ctx, qout[0], qout[1], qout[2], diag_out, s);
     return CS_OK;
 }
@@ -86,7 +86,7 @@ extern "C" int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double
         // a single-stage scheme has nothing else to read from, so it goes through scratch
         void** dst = (k == ns - 1 && ns > 1) ? q0 : (k % 2 == 0 ? ctx->qa : ctx->qb);
         if ((rc = cs_launch_stage(ctx, q0, cur, dst, pr[k].a, pr[k].b, dt, 2, nullptr, s))) return rc;
-        if ((rc = cs_launch_halo(ctx, dst[0], dst[1], dst[2], 3, s))) return rc;
+        if (!ctx->stage_pushed && (rc = cs_launch_halo(ctx, dst[0], dst[1], dst[2], 3, s))) return rc;
         for (int c = 0; c < 3; ++c) cur[c] = dst[c];
     }
     if (ns == 1)

@@ -53,6 +53,7 @@ struct cs_ctx {
     void* d_rot = nullptr;                       // optional [n_local][4] rotation (state dtype)
     int4* d_push = nullptr;                      // [T][4] (dst local tile or -1, dst edge, reverse, code)
     bool push_complete = false;                  // every neighbour tile is local
+    bool stage_pushed = false;                   // the last stage launch stored the edge ghosts itself
 
     // sharded exchange
     std::vector<PeerPlan> peers;

@@ -66,7 +66,7 @@ StageParams<R> make_params(cs_ctx* ctx, const void* const q0[3], const void* con
     P.topo = ctx->has_topo ? (const R*)ctx->topo : nullptr;
     P.xt = (const R*)ctx->d_xt;
     P.ainv = (const R*)ctx->d_ainv;
-    P.push = nullptr;
+    P.push = nullptr;        // set by the marching launcher when the halo is fused into the stage
     P.partials = nullptr;
     P.n = ctx->n, P.g = ctx->g, P.m = ctx->m, P.p = ctx->p, P.T = ctx->T, P.t0 = ctx->t0;
     P.part = part;
@@ -150,9 +150,12 @@ MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m,
 
 template <typename R, int V, int LIM, int MINB>
 int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_t s) {
-    const MarchGeom G = march_geometry(ctx, stage_march_kernel<R, V, LIM, MINB>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
+    const MarchGeom G = march_geometry(ctx, stage_march_kernel<R, V, LIM, MINB, false>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
     const int warps = CS_MARCH_THREADS / 32;
-    stage_march_kernel<R, V, LIM, MINB><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, 0, s>>>(P, G);
+    if (P.push)
+        stage_march_kernel<R, V, LIM, MINB, true><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, 0, s>>>(P, G);
+    else
+        stage_march_kernel<R, V, LIM, MINB, false><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, 0, s>>>(P, G);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;
@@ -182,6 +185,7 @@ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 
 template <typename R, int LIM>
 int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
     const int n = P.n, g = P.g;
+    ctx->stage_pushed = false;
     if (part == 1) return launch_rim<R, LIM>(ctx, P, s);
     const int lo = part == 0 ? g : 0, hi = part == 0 ? n - g : n;
     if (hi <= lo) return CS_OK;
@@ -205,17 +209,23 @@ int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
             return launch_tma<R, 2, LIM, 2>(ctx, P, lo, hi, s);
         }
     }
+    StageParams<R> Q = P;
+    ctx->stage_pushed = false;
+    if (part == 2 && ctx->cfg.fused_halo && ctx->push_complete && ctx->d_push && !ctx->d_rot && env_int("CS_FUSED_HALO", 1)) {
+        Q.push = ctx->d_push;
+        ctx->stage_pushed = true;   // the caller can skip the ghost-fill launch (corner blocks are not refreshed)
+    }
     const int occ = env_int("CS_MARCH_OCC", 0);
     if constexpr (sizeof(R) == 4) {
         const int vec = env_int("CS_MARCH_VEC", 4);
         if (vec == 4 && P.m % 4 == 0 && ((size_t)P.m * sizeof(R)) % 16 == 0) {
-            if (occ == 3) return launch_march<R, 4, LIM, 3>(ctx, P, lo, hi, s);
-            return launch_march<R, 4, LIM, 2>(ctx, P, lo, hi, s);
+            if (occ == 3) return launch_march<R, 4, LIM, 3>(ctx, Q, lo, hi, s);
+            return launch_march<R, 4, LIM, 2>(ctx, Q, lo, hi, s);
         }
-        return launch_march<R, 2, LIM, 4>(ctx, P, lo, hi, s);
+        return launch_march<R, 2, LIM, 4>(ctx, Q, lo, hi, s);
     } else {
-        if (occ == 3) return launch_march<R, 2, LIM, 3>(ctx, P, lo, hi, s);
-        return launch_march<R, 2, LIM, 2>(ctx, P, lo, hi, s);
+        if (occ == 3) return launch_march<R, 2, LIM, 3>(ctx, Q, lo, hi, s);
+        return launch_march<R, 2, LIM, 2>(ctx, Q, lo, hi, s);
     }
 }
 

@@ -126,6 +126,46 @@ __device__ __forceinline__ void march_derive(const StageParams<R>& P, const Marc
     }
 }
 
+// Fused halo: a freshly computed boundary cell is also stored into the ghost cell of the neighbouring
+// tile that mirrors it (same index mapping and signed permutation as the halo kernel, read from the
+// per-(tile, edge) descriptor), so no separate ghost-fill launch is needed after the stage.
+// A PushMap is that mapping for one (edge, depth): the ghost of the cell at along-edge index k lives at
+// element offset base + k * stride.  e: 0 N, 1 S, 2 E, 3 W.
+struct PushMap {
+    unsigned base;
+    int stride;
+    int code;      // -1: the neighbour is not on this device (no push)
+};
+
+template <typename R>
+__device__ __forceinline__ PushMap march_push_map(const StageParams<R>& P, int t, int e, int d) {
+    const int4 pd = P.push[t * 4 + e];                    // (dst tile or -1, dst edge, reverse, code)
+    PushMap pm;
+    pm.code = pd.x < 0 ? -1 : pd.w;
+    const int n = P.n, g = P.g, m = P.m;
+    const int sgn = pd.z ? -1 : 1, k0 = pd.z ? n - 1 : 0;     // k -> k0 + sgn * k along the destination edge
+    const unsigned tile = (unsigned)max(pd.x, 0) * m * m;
+    if (pd.y < 2) {
+        const int dj = pd.y == 0 ? g + n + d : g - 1 - d;
+        pm.base = tile + (unsigned)dj * m + g + k0;
+        pm.stride = sgn;
+    } else {
+        const int di = pd.y == 2 ? g + n + d : g - 1 - d;
+        pm.base = tile + (unsigned)(g + k0) * m + di;
+        pm.stride = sgn * m;
+    }
+    return pm;
+}
+
+template <typename R>
+__device__ __forceinline__ void march_push_store(const StageParams<R>& P, const PushMap& pm, int k, R h, R u, R v) {
+    const unsigned o = pm.base + (unsigned)(k * pm.stride);
+    const R x = (pm.code & 1) ? v : u, y = (pm.code & 1) ? u : v;
+    P.ho[o] = h;
+    P.uo[o] = (pm.code & 2) ? -x : x;
+    P.vo[o] = (pm.code & 4) ? -y : y;
+}
+
 // x direction, tendencies and RK combination of one row segment (shared by the LDG-fed and the
 // TMA-fed kernels).  Each lane computes the half slopes of its own V cells and the V faces on
 // their left; the neighbour's slope and the right-most face come by shuffle, so no slope or flux
@@ -187,7 +227,7 @@ __device__ __forceinline__ void march_row_update(const StageParams<R>& P, const 
     }
 }
 
-template <typename R, int V, int LIM, int MINB>
+template <typename R, int V, int LIM, int MINB, bool PUSH>
 __global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
 stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant__ MarchGeom G) {
     const int lane = threadIdx.x & 31;
@@ -228,6 +268,20 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
             const int i = col0 + c - g;
             om[c] = lane_out && i >= G.xlo && i < G.xhi;
             all_out = all_out && om[c];
+        }
+    }
+    // fused halo: only the first / last chunk of a row holds columns within g of the tile's W / E edge.
+    // A lane's edge columns share one ghost mapping up to the depth: depth d adds d * ew_dstep elements.
+    const bool edge_warp = PUSH && (chunk == 0 || chunk == G.nchunks - 1);
+    PushMap ew;
+    int ew_dstep = 0;
+    ew.code = -1;
+    if constexpr (PUSH) {
+        const int i0 = col0 - g, i1 = col0 + V - 1 - g;              // interior index of the first / last column
+        if (edge_warp && lane_out && (i0 < g || i1 >= P.n - g)) {
+            const int e = i0 < g ? 3 : 2;
+            ew = march_push_map<R>(P, t, e, 0);
+            ew_dstep = (int)(march_push_map<R>(P, t, e, 1).base - ew.base);
         }
     }
     const unsigned tbase = (unsigned)t * m * m + col0;   // shards are < 2^31 elements (checked at create)
@@ -331,6 +385,28 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
 #pragma unroll
             for (int c = 0; c < V; ++c)
                 if (om[c]) P.ho[oJ + c] = oh[c], P.uo[oJ + c] = ou[c], P.vo[oJ + c] = ov[c];
+        }
+        if constexpr (PUSH) {
+            const int j = J - g;
+            if (j < g || j >= P.n - g) {                  // whole row lies in the S / N boundary band
+                const PushMap pm = march_push_map<R>(P, t, j < g ? 1 : 0, j < g ? j : P.n - 1 - j);
+                if (pm.code >= 0) {
+#pragma unroll
+                    for (int c = 0; c < V; ++c)
+                        if (om[c]) march_push_store<R>(P, pm, col0 + c - g, oh[c], ou[c], ov[c]);
+                }
+            }
+            if (edge_warp && ew.code >= 0) {
+#pragma unroll
+                for (int c = 0; c < V; ++c) {
+                    const int i = col0 + c - g, d = i < g ? i : P.n - 1 - i;
+                    if (om[c] && d < g) {
+                        PushMap pm = ew;
+                        pm.base += (unsigned)(d * ew_dstep);
+                        march_push_store<R>(P, pm, j, oh[c], ou[c], ov[c]);
+                    }
+                }
+            }
         }
 
         // slide the raw-row window one row north

@@ -220,7 +220,7 @@ class Context:
     """Owns one ``cs_ctx`` (C ABI) for a contiguous tile range on one CUDA device."""
 
     def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f64", rk="ssprk3", limiter="mc", advect_only=False,
-                 device=0, tile_begin=0, tile_count=0, kernel="auto", fused_halo=True, radius=0.0, omega=0.0,
+                 device=0, tile_begin=0, tile_count=0, kernel="auto", fused_halo=False, radius=0.0, omega=0.0,
                  gravity=0.0, axis=(0.0, 0.0, 1.0), tangents=None):
         self._lib = B.lib()
         self.dtype = _torch_dtype(dtype)
@@ -446,7 +446,7 @@ def make_halo_exchange(schedule, N, *, halo=1, tiles_per_edge=1, dtype="f64", de
 
 
 def make_step(N, *, tiles_per_edge=1, halo=2, dtype="f64", rk="ssprk3", limiter="mc", advect_only=False,
-              device=0, hs=None, axis=(0.0, 0.0, 1.0), kernel="auto", fused_halo=True, tangents=None, **phys):
+              device=0, hs=None, axis=(0.0, 0.0, 1.0), kernel="auto", fused_halo=False, tangents=None, **phys):
     """Return ``step(state, dt) -> state`` for a single-device run (all 6 p^2 tiles on ``device``).
 
     ``state`` is a dict ``{'h', 'u', 'v'}`` of halo-filled CUDA tensors ``[6 p^2, n + 2g, n + 2g]``;

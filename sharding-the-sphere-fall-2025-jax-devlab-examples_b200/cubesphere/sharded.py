@@ -3,12 +3,13 @@
 world == 1: every tile lives on one device and the whole step is ``cs_step`` (halo included).
 world  > 1: each rank owns ``6 p^2 / world`` consecutive tiles.  Per RK stage
 
-    rim cells   (those a peer's ghosts depend on)  -> stage kernel, part 1
-    pack        boundary cells peers need           -> one kernel
-    all-to-all  NCCL over NVLink, on a side stream   } overlapped with
-    inner cells                                     -> stage kernel, part 0  }
-    local ghosts (same-rank neighbours)             -> halo kernel
-    unpack      received cells into remote ghosts   -> one kernel
+    side stream                                          main stream
+    rim cells (what ghosts depend on)  stage kernel, part 1   inner cells: stage kernel, part 0
+    same-rank ghosts                   halo kernel            (almost all of the time)
+    pack boundary cells peers need     one kernel
+    all-to-all                         NCCL over NVLink
+    unpack into remote ghosts          one kernel
+    ------------------------------ join at the end of the stage ------------------------------
 
 The partition is the reference's: axis 0 block-sharded over a 1-D mesh
 (reference JAX-DevLab-Examples.py:40-57, 77-79).
@@ -127,12 +128,15 @@ class ShardedStepper:
             last = k == len(pairs) - 1 and len(pairs) > 1
             out = q0 if last else (self.qa if k % 2 == 0 else self.qb)
             if self.overlap:
-                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1)              # rim first
+                # side stream: rim cells -> same-rank ghosts -> pack -> all-to-all -> unpack;
+                # main stream: the inner cells, which is where the time goes.  Both start as soon as the
+                # previous stage is complete and write disjoint cells; they join at the end of the stage.
                 self.comm_stream.wait_stream(main)
                 with torch.cuda.stream(self.comm_stream):
+                    self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1)
+                    self.ctx.halo_fill_state(*out)
                     self._exchange(*out)
-                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=0)              # inner cells meanwhile
-                self.ctx.halo_fill_state(*out)                                 # same-rank ghosts
+                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=0)
                 main.wait_stream(self.comm_stream)
             else:
                 self.ctx.rk_stage(q0, cur, out, a, b, dt, part=2)

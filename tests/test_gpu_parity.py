@@ -313,3 +313,30 @@ def test_sharded_contexts_emulated_on_one_gpu(built_library, p, world):
                 assert np.linalg.norm(a_[sl] - w_[sl]) <= 1e-13 * np.linalg.norm(w_[sl])
     for ctx in ctxs:
         ctx.close()
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-13), (np.float32, 2e-5)])
+@pytest.mark.parametrize("p", [1, 2])
+def test_fused_halo_push_matches_halo_kernel(built_library, dtype, tol, p):
+    """fused_halo=1: the stage kernel stores boundary cells straight into the neighbours' edge ghosts
+    (no halo launch).  Same interiors and same edge ghosts as the default path; corner blocks excluded."""
+    N, g = 48, 2
+    case = cases.make_case("tc5", N)
+    par = orc.Params(N, g, axis=case.axis, hs=case.hs)
+    ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
+    dt = cases.stable_dt(case)
+    res = []
+    for fused in (False, True):
+        ctx = api.Context(N, tiles_per_edge=p, halo=g, dtype=dtype, axis=case.axis, tangents=orc.centre_tangents(N), fused_halo=fused)
+        dev = [torch.from_numpy(orc.faces_to_tiles(x, p, g).astype(dtype)).cuda() for x in ref]
+        ctx.set_topography(torch.from_numpy(orc.faces_to_tiles(par.hs, p, g).astype(dtype)).cuda())
+        l0 = ctx.launches
+        for _ in range(4):
+            ctx.step(*dev, dt)
+        assert ctx.launches - l0 == (12 if fused else 24)          # 3 stages (+ 3 halo fills) per step
+        res.append([x.cpu().numpy().astype(np.float64) for x in dev])
+        ctx.close()
+    n = N // p
+    for a, b in zip(*res):
+        for sl in ((slice(None), slice(g, g + n), slice(None)), (slice(None), slice(None), slice(g, g + n))):
+            assert np.linalg.norm(a[sl] - b[sl]) <= tol * np.linalg.norm(a[sl])
