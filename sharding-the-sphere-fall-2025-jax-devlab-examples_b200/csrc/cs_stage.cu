@@ -129,7 +129,11 @@ MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m,
         it = occupancy.emplace(key, bps).first;
     }
     const int blocks_per_sm = it->second;
-    const long long slots = (long long)ctx->num_sms * blocks_per_sm * (CS_MARCH_THREADS / 32);
+    // the inner part of a split stage (lo > 0) shares the GPU with the rim / pack / NCCL kernels of the side
+    // stream: leave them a few SMs, otherwise the displaced warps form a second wave
+    const int reserve = lo > 0 ? env_int("CS_MARCH_RESERVE_SMS", 12) : 0;
+    const int sms = ctx->num_sms - reserve > 8 ? ctx->num_sms - reserve : ctx->num_sms;
+    const long long slots = (long long)sms * blocks_per_sm * (CS_MARCH_THREADS / 32);
     const int span = hi - lo;
     int best_rows = span < 8 ? span : 8;
     double best_cost = 1e300;
