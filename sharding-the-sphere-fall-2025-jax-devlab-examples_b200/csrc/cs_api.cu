@@ -1,4 +1,6 @@
 // Entry points that compose the kernels: topography, one RK stage, one step, host-buffer step.
+#include <cstdlib>
+
 #include "cs_internal.cuh"
 
 namespace {
@@ -67,16 +69,11 @@ extern "C" int cs_rk_stage(cs_ctx* ctx, const void* const q0[3], const void* con
     return CS_OK;
 }
 
-extern "C" int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out, void* stream) {
-    if (!ctx || !h || !u || !v) return cs_fail(ctx, CS_E_INVALID, "cs_step: NULL argument");
-    int rc = check_step_ready(ctx, "cs_step");
-    if (rc) return rc;
-    if (!single_device(ctx))
-        return cs_fail(ctx, CS_E_INVALID,
-                       "cs_step: the context owns %d of %d tiles; drive shards with cs_rk_stage_part + cs_halo_pack/unpack",
-                       ctx->T, ctx->T_all);
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
-    cudaStream_t s = (cudaStream_t)stream;
+namespace {
+
+// The launches of one step, in order, on stream s.
+int enqueue_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out, cudaStream_t s) {
+    int rc;
     RkPair pr[3];
     const int ns = rk_pairs(ctx->cfg.rk, pr);
     void* q0[3] = {h, u, v};
@@ -94,6 +91,84 @@ extern "C" int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double
             CS_CUDA(ctx, cudaMemcpyAsync(q0[c], ctx->qa[c], ctx->field_elems * ctx->esize, cudaMemcpyDeviceToDevice, s));
     if (diag_out) return cs_launch_diag(ctx, h, u, v, diag_out, s);
     return CS_OK;
+}
+
+// A step is 6-7 short launches; replaying them as one CUDA graph removes the gaps between them.
+// Graphs are keyed by the arguments that are baked into the kernels' parameters.
+StepGraph* find_or_capture(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out) {
+    for (StepGraph& g : ctx->graphs)
+        if (g.exec && g.h == h && g.u == u && g.v == v && g.dt == dt && g.diag == diag_out && g.topo == ctx->has_topo) {
+            g.stamp = ++ctx->graph_clock;
+            return &g;
+        }
+    if (!ctx->cap_stream && cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    StepGraph* slot = nullptr;                            // an empty slot, else the least recently used one
+    for (StepGraph& g : ctx->graphs)
+        if (!g.exec) {
+            slot = &g;
+            break;
+        }
+    if (!slot) {
+        slot = &ctx->graphs[0];
+        for (StepGraph& g : ctx->graphs)
+            if (g.stamp < slot->stamp) slot = &g;
+    }
+    if (slot->exec) cudaGraphExecDestroy(slot->exec), slot->exec = nullptr;
+    const int64_t l0 = ctx->launches;
+    if (cudaStreamBeginCapture(ctx->cap_stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    const int rc = enqueue_step(ctx, h, u, v, dt, diag_out, ctx->cap_stream);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(ctx->cap_stream, &graph);
+    const int64_t n = ctx->launches - l0;
+    ctx->launches = l0;                                   // capturing is not launching
+    if (rc != CS_OK || e != cudaSuccess || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        return nullptr;
+    }
+    const cudaError_t ei = cudaGraphInstantiate(&slot->exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ei != cudaSuccess) {
+        cudaGetLastError();
+        slot->exec = nullptr;
+        return nullptr;
+    }
+    slot->h = h, slot->u = u, slot->v = v, slot->dt = dt, slot->diag = diag_out, slot->topo = ctx->has_topo;
+    slot->launches = n;
+    slot->stamp = ++ctx->graph_clock;
+    return slot;
+}
+
+}  // namespace
+
+extern "C" int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out, void* stream) {
+    if (!ctx || !h || !u || !v) return cs_fail(ctx, CS_E_INVALID, "cs_step: NULL argument");
+    int rc = check_step_ready(ctx, "cs_step");
+    if (rc) return rc;
+    if (!single_device(ctx))
+        return cs_fail(ctx, CS_E_INVALID,
+                       "cs_step: the context owns %d of %d tiles; drive shards with cs_rk_stage_part + cs_halo_pack/unpack",
+                       ctx->T, ctx->T_all);
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    // graph replay unless the caller is itself capturing this stream (no nested capture) or opted out
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cap) != cudaSuccess) cudaGetLastError(), cap = cudaStreamCaptureStatusNone;
+    static const bool want_graph = []() { const char* e = std::getenv("CS_STEP_GRAPH"); return !(e && *e == '0'); }();
+    if (want_graph && cap == cudaStreamCaptureStatusNone) {
+        if (StepGraph* g = find_or_capture(ctx, h, u, v, dt, diag_out)) {
+            CS_CUDA(ctx, cudaGraphLaunch(g->exec, s));
+            ctx->launches += g->launches;
+            return CS_OK;
+        }
+    }
+    return enqueue_step(ctx, h, u, v, dt, diag_out, s);
 }
 
 extern "C" int cs_step_host(cs_ctx* ctx, void* h_host, void* u_host, void* v_host, double dt, int nsteps, double* diag_host,

@@ -169,6 +169,9 @@ extern "C" int cs_ctx_destroy(cs_ctx* ctx) {
     if (!ctx) return CS_OK;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
+    for (StepGraph& g : ctx->graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
     void* ptrs[] = {ctx->d_xt, ctx->d_ainv, ctx->d_xt64, ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, ctx->d_rot, ctx->d_push,
                     ctx->d_send_src, ctx->d_recv_dst, ctx->d_recv_code, ctx->d_send_off, ctx->d_recv_off, ctx->qa[0], ctx->qa[1], ctx->qa[2],
                     ctx->qb[0], ctx->qb[1], ctx->qb[2], ctx->topo, ctx->host_state[0], ctx->host_state[1], ctx->host_state[2], ctx->d_partials, ctx->d_diag, ctx->d_ticket};

@@ -25,6 +25,16 @@ struct PeerPlan {
     int64_t send_offset = 0, recv_offset = 0;    // cells, prefix sums over peers
 };
 
+struct StepGraph {            // one captured step, keyed by what is baked into its kernel parameters
+    cudaGraphExec_t exec = nullptr;
+    void *h = nullptr, *u = nullptr, *v = nullptr;
+    double dt = 0.0;
+    double* diag = nullptr;
+    bool topo = false;
+    int64_t launches = 0;
+    uint64_t stamp = 0;
+};
+
 struct cs_ctx {
     cs_config cfg;
     int N = 0, p = 0, n = 0, g = 0, m = 0;
@@ -76,6 +86,10 @@ struct cs_ctx {
     int partial_cap = 0;
     double* d_diag = nullptr;                    // [2]
     unsigned int* d_ticket = nullptr;
+
+    StepGraph graphs[4];
+    uint64_t graph_clock = 0;
+    cudaStream_t cap_stream = nullptr;
 
     mutable std::string err;
     int64_t launches = 0;

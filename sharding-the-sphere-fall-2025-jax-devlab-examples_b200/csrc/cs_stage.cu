@@ -228,6 +228,7 @@ int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
         }
         return launch_march<R, 2, LIM, 4>(ctx, Q, lo, hi, s);
     } else {
+        if (env_int("CS_MARCH_VEC", 2) == 1) return launch_march<R, 1, LIM, 4>(ctx, Q, lo, hi, s);
         if (occ == 3) return launch_march<R, 2, LIM, 3>(ctx, Q, lo, hi, s);
         return launch_march<R, 2, LIM, 2>(ctx, Q, lo, hi, s);
     }

@@ -24,10 +24,9 @@ def main():
             ctx.halo_fill_state(h, u, v)
             out = [ctx.new_field() for _ in range(3)]
             q0 = [x.clone() for x in (h, u, v)]          # distinct arrays: in a real step q0 != qs for stages 2, 3
-            if kernel == "march":
-                combos = [(v_, r_, o_, pf) for (v_, o_) in (((4, 2),) if dtype == "f32" else ((2, 2),)) for r_ in ((0, 64, 104, 128) if dtype == "f32" else (0, 32, 48, 52, 64)) for pf in (2,)]
-            else:
-                combos = [(v_, r_, 0, g_) for v_ in ((2, 4) if dtype == "f32" else (1, 2)) for r_ in (16, 32, 64) for g_ in (5, 8)]
+            if dtype == "f32":
+                continue
+            combos = [(1, 0, 0, 2), (1, 32, 0, 2), (1, 64, 0, 2), (2, 0, 2, 2)]
             for vec, rows, occ, ring in combos:
                 if True:
                     os.environ["CS_MARCH_VEC"], os.environ["CS_MARCH_OCC"], os.environ["CS_TMA_RING"] = str(vec or 4), str(occ), str(ring or 6)
