@@ -9,7 +9,8 @@ world  > 1: each rank owns ``6 p^2 / world`` consecutive tiles.  Per RK stage
     pack boundary cells peers need     one kernel
     all-to-all                         NCCL over NVLink
     unpack into remote ghosts          one kernel
-    ------------------------------ join at the end of the stage ------------------------------
+    Inner cells never read ghosts: stage k+1's inner kernel waits for stage k's inner and rim kernels
+    only, the exchange has a whole stage of slack; the streams join at the end of the step.
 
 The partition is the reference's: axis 0 block-sharded over a 1-D mesh
 (reference JAX-DevLab-Examples.py:40-57, 77-79).
@@ -124,25 +125,39 @@ class ShardedStepper:
         cur = q0
         pairs = RK_PAIRS[self.rk]
         main = torch.cuda.current_stream(self.device)
+        ev_rim = ev_inner = None
         for k, (a, b) in enumerate(pairs):
             last = k == len(pairs) - 1 and len(pairs) > 1
             out = q0 if last else (self.qa if k % 2 == 0 else self.qb)
             if self.overlap:
                 # side stream: rim cells -> same-rank ghosts -> pack -> all-to-all -> unpack;
-                # main stream: the inner cells, which is where the time goes.  Both start as soon as the
-                # previous stage is complete and write disjoint cells; they join at the end of the stage.
-                self.comm_stream.wait_stream(main)
+                # main stream: the inner cells, which is where the time goes.
+                # Inner cells never read a ghost cell, so stage k+1's inner kernel only waits for stage k's
+                # inner and rim kernels -- not for its exchange, which gets a whole stage of slack and is
+                # needed by stage k+1's rim kernel alone.  The two streams join at the end of the step.
                 with torch.cuda.stream(self.comm_stream):
+                    if ev_inner is None:
+                        self.comm_stream.wait_stream(main)                     # whatever came before the step
+                    else:
+                        self.comm_stream.wait_event(ev_inner)                  # rim reads inner cells next to it
                     self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1)
+                    ev_rim_new = torch.cuda.Event()
+                    ev_rim_new.record(self.comm_stream)
                     self.ctx.halo_fill_state(*out)
                     self._exchange(*out)
+                if ev_rim is not None:
+                    main.wait_event(ev_rim)                                    # inner reads the previous rim cells
                 self.ctx.rk_stage(q0, cur, out, a, b, dt, part=0)
-                main.wait_stream(self.comm_stream)
+                ev_inner = torch.cuda.Event()
+                ev_inner.record(main)
+                ev_rim = ev_rim_new
             else:
                 self.ctx.rk_stage(q0, cur, out, a, b, dt, part=2)
                 self.ctx.halo_fill_state(*out)
                 self._exchange(*out)
             cur = out
+        if self.overlap:
+            main.wait_stream(self.comm_stream)
         if len(pairs) == 1:
             for x, y in zip(q0, cur):
                 x.copy_(y)
