@@ -35,23 +35,34 @@ __device__ __forceinline__ void block_sum2(double& a, double& b) {
 template <typename R>
 __global__ void __launch_bounds__(DIAG_THREADS)
 diag_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restrict__ v, const R* __restrict__ topo,
-            const double* __restrict__ xt, int n, int g, int m, int p, int T, int t0, double a2, double grav, double darea,
+            const double* __restrict__ xt, int n, int g, int m, int p, int T, int t0, int rows_per_block, double a2, double grav,
+            double darea,
             double* __restrict__ partials, unsigned int* __restrict__ ticket, double* __restrict__ out) {
+    // a block owns `rows_per_block` consecutive rows of one tile (no integer division per cell);
+    // threads run along x, so loads are coalesced and every thread's summation order is fixed
     double mass = 0.0, energy = 0.0;
-    const int64_t cells = (int64_t)T * n * n;
-    for (int64_t c = blockIdx.x * (int64_t)DIAG_THREADS + threadIdx.x; c < cells; c += (int64_t)gridDim.x * DIAG_THREADS) {
-        const int t = (int)(c / ((int64_t)n * n));
-        const int r = (int)(c - (int64_t)t * n * n);
-        const int j = r / n, i = r - j * n;
+    const int blocks_per_tile = (n + rows_per_block - 1) / rows_per_block;
+    for (int b = blockIdx.x; b < T * blocks_per_tile; b += gridDim.x) {
+        const int t = b / blocks_per_tile;
+        const int j0 = (b - t * blocks_per_tile) * rows_per_block;
+        const int j1 = min(j0 + rows_per_block, n);
         const TileCoord tc = cs_tile_coord(t + t0, p);
-        const size_t o = (size_t)t * m * m + (size_t)(j + g) * m + (i + g);
-        const Metric<double> M = cs_metric<double>(xt[tc.tx * n + i + g], xt[tc.ty * n + j + g], a2);
-        const double hh = (double)h[o], uu = (double)u[o], vv = (double)v[o];
-        const double hs = topo ? (double)topo[o] : 0.0;
-        const Derived<double> D = cs_derive<double>(M, hh, uu, vv, hs, grav);
-        const double w = M.sg * darea;
-        mass += w * hh;
-        energy += w * (hh * D.K + 0.5 * grav * hh * hh + grav * hh * hs);
+        const double* xt_x = xt + tc.tx * n + g;
+        const double* xt_y = xt + tc.ty * n + g;
+        for (int j = j0; j < j1; ++j) {
+            const double Y = xt_y[j];
+            const size_t row = (size_t)t * m * m + (size_t)(j + g) * m + g;
+            for (int i = threadIdx.x; i < n; i += DIAG_THREADS) {
+                const size_t o = row + i;
+                const Metric<double> M = cs_metric<double>(xt_x[i], Y, a2);
+                const double hh = (double)h[o], uu = (double)u[o], vv = (double)v[o];
+                const double hs = topo ? (double)topo[o] : 0.0;
+                const Derived<double> D = cs_derive<double>(M, hh, uu, vv, hs, grav);
+                const double w = M.sg * darea;
+                mass += w * hh;
+                energy += w * (hh * D.K + 0.5 * grav * hh * hh + grav * hh * hs);
+            }
+        }
     }
     block_sum2(mass, energy);
     __shared__ bool last;
@@ -80,22 +91,22 @@ diag_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restric
 }  // namespace
 
 int cs_launch_diag(cs_ctx* ctx, const void* h, const void* u, const void* v, double* out, cudaStream_t s) {
-    const int64_t cells = (int64_t)ctx->T * ctx->n * ctx->n;
-    int64_t blocks = (cells + DIAG_THREADS * 4 - 1) / (DIAG_THREADS * 4);
-    const int64_t cap = std::min<int64_t>(ctx->partial_cap, (int64_t)ctx->num_sms * 8);
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
+    // about 8 blocks per SM, each a whole number of rows of one tile
+    const int64_t want = std::min<int64_t>(ctx->partial_cap, (int64_t)ctx->num_sms * 8);
+    int rows_per_block = (int)(((int64_t)ctx->T * ctx->n + want - 1) / want);
+    if (rows_per_block < 1) rows_per_block = 1;
+    const int64_t blocks = std::min<int64_t>(want, (int64_t)ctx->T * ((ctx->n + rows_per_block - 1) / rows_per_block));
     const double a2 = ctx->radius * ctx->radius, darea = ctx->delta * ctx->delta;
     if (ctx->dtype == CS_F64)
         diag_kernel<double><<<(int)blocks, DIAG_THREADS, 0, s>>>((const double*)h, (const double*)u, (const double*)v,
                                                                 ctx->has_topo ? (const double*)ctx->topo : nullptr, ctx->d_xt64,
-                                                                ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, a2, ctx->gravity,
-                                                                darea, ctx->d_partials, ctx->d_ticket, out);
+                                                                ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, rows_per_block, a2,
+                                                                ctx->gravity, darea, ctx->d_partials, ctx->d_ticket, out);
     else
         diag_kernel<float><<<(int)blocks, DIAG_THREADS, 0, s>>>((const float*)h, (const float*)u, (const float*)v,
                                                                ctx->has_topo ? (const float*)ctx->topo : nullptr, ctx->d_xt64,
-                                                               ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, a2, ctx->gravity,
-                                                               darea, ctx->d_partials, ctx->d_ticket, out);
+                                                               ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, rows_per_block, a2,
+                                                               ctx->gravity, darea, ctx->d_partials, ctx->d_ticket, out);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;
