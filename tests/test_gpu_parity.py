@@ -340,3 +340,67 @@ def test_fused_halo_push_matches_halo_kernel(built_library, dtype, tol, p):
     for a, b in zip(*res):
         for sl in ((slice(None), slice(g, g + n), slice(None)), (slice(None), slice(None), slice(g, g + n))):
             assert np.linalg.norm(a[sl] - b[sl]) <= tol * np.linalg.norm(a[sl])
+
+
+def _run_case_c_oracle(name, N, nsteps, dtype=np.float64, p=1, **kw):
+    """Like _run_case but against the C/OpenMP port of the oracle (bit-identical to the NumPy one,
+    tests/test_oracle.py), which makes BASELINE.json's full sizes affordable."""
+    from oracle import cs_oracle_c as occ
+    g = 2
+    case = cases.make_case(name, N, **kw)
+    hs = orc.halo_fill_scalar(orc.pad(case.hs, g), g) if case.hs is not None else None
+    co = occ.COracle(N, g, axis=case.axis, advect_only=case.advect_only, hs=hs)
+    ref = [np.ascontiguousarray(x) for x in orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)]
+    ctx = api.Context(N, tiles_per_edge=p, halo=g, dtype=dtype, advect_only=case.advect_only, axis=case.axis,
+                      tangents=orc.centre_tangents(N))
+    dev = [torch.from_numpy(orc.faces_to_tiles(x, p, g).astype(dtype)).cuda() for x in ref]
+    if hs is not None:
+        ctx.set_topography(torch.from_numpy(orc.faces_to_tiles(hs, p, g).astype(dtype)).cuda())
+    dt = cases.stable_dt(case)
+    m0 = ctx.diagnostics(*dev).cpu().numpy()
+    for _ in range(nsteps):
+        ctx.step(*dev, dt)
+    co.step(*ref, dt, nsteps)
+    m1 = ctx.diagnostics(*dev).cpu().numpy()
+    got = [orc.tiles_to_faces(x.cpu().numpy().astype(np.float64), p, g) for x in dev]
+    c = slice(g, g + N)
+    errs = [np.linalg.norm(a[:, c, c] - b[:, c, c]) / max(np.linalg.norm(b[:, c, c]), 1e-300) for a, b in zip(got, ref)]
+    mo = co.diagnostics(*ref)
+    ctx.close()
+    return errs, m0, m1, mo
+
+
+def test_config_tc1_c192_fp64_bell_over_a_corner(built_library):
+    """BASELINE configs[1]: cosine bell, C192 fp64, 100 steps, flow tilted by 45 degrees so the bell
+    heads over a cube corner (every seam orientation and the corner ghosts are exercised)."""
+    errs, m0, m1, mo = _run_case_c_oracle("tc1", 192, 100, alpha0=np.pi / 4)
+    assert errs[0] <= 1e-12, errs
+    assert abs(m1[0] - m0[0]) <= 1e-13 * m0[0] and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
+
+
+def test_config_tc5_c384_fp64_tiles(built_library):
+    """BASELINE configs[2]: flow over the mountain, C384 fp64, 24 tiles (p = 2, the 8-GPU tiling), 100 steps."""
+    errs, m0, m1, mo = _run_case_c_oracle("tc5", 384, 100, p=2)
+    assert errs[0] <= 1e-12, errs
+    assert abs(m1[0] - m0[0]) <= 1e-13 * m0[0] and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
+
+
+def test_config_tc6_c768_fp32_vs_fp64(built_library):
+    """BASELINE configs[3]: Rossby-Haurwitz wave, C768, fp64 against the oracle and fp32 reported beside it."""
+    errs64, m0, m1, mo = _run_case_c_oracle("tc6", 768, 20)
+    assert errs64[0] <= 1e-12, errs64
+    assert abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
+    errs32, m0, m1, _ = _run_case_c_oracle("tc6", 768, 20, dtype=np.float32)
+    print("C768 fp32 vs fp64 oracle after 20 steps, rel L2 (h, u, v):", errs32)
+    assert errs32[0] <= 2e-5, errs32
+    assert abs(m1[0] - m0[0]) <= 1e-6 * m0[0]
+
+
+def test_config_galewsky_c1536_against_oracle(built_library):
+    """BASELINE configs[4] at full size: 5 steps of the Galewsky jet at C1536, fp64 to 1e-12 and fp32 to 2e-5."""
+    errs64, m0, m1, mo = _run_case_c_oracle("galewsky", 1536, 5)
+    assert errs64[0] <= 1e-12, errs64
+    assert abs(m1[0] - m0[0]) <= 1e-13 * m0[0] and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
+    errs32, _, _, _ = _run_case_c_oracle("galewsky", 1536, 5, dtype=np.float32)
+    print("C1536 fp32 vs fp64 oracle after 5 steps, rel L2 (h, u, v):", errs32)
+    assert errs32[0] <= 2e-5, errs32
