@@ -88,9 +88,13 @@ class ShardedStepper:
         return h, u, v
 
     def set_topography(self, hs):
-        self.ctx.set_topography(hs)
+        """``hs``: this rank's tiles of the bottom topography (interiors set; ghosts are filled here,
+        from same-rank neighbours by the halo kernel and from peers by a one-field exchange)."""
         if self.world > 1:
-            raise NotImplementedError("topography on sharded runs: fill hs ghosts before sharding")
+            hs = hs.clone()
+            self.ctx.halo_fill_scalar(hs)
+            self._exchange(hs, None, None, nfields=1)
+        self.ctx.set_topography(hs)
 
     # -- step -------------------------------------------------------------------------------
     def step(self, h, u, v, dt):

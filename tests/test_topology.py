@@ -145,3 +145,19 @@ def test_push_descriptors_consistent_with_table():
                     dj, di = {0: (g + n + d, g + kk), 1: (g - 1 - d, g + kk),
                               2: (g + kk, g + n + d), 3: (g + kk, g - 1 - d)}[de]
                     assert key[(dt_, dj, di)] == (t, sj, si, code)
+
+
+def test_load_config_defaults_and_validation(tmp_path):
+    from cubesphere import config
+    cfg = config.load_config()
+    assert cfg["parallelization"] == {"tiles_per_edge": 1, "num_devices": 6, "device_type": "cpu"}   # PY:22-24
+    cfg = config.load_config({"parallelization": {"tiles_per_edge": 2, "num_devices": 8}, "extra": {"a": 1}})
+    assert cfg["parallelization"]["tiles_per_edge"] == 2 and cfg["extra"] == {"a": 1}
+    mesh, sh = api.setup_sharding(cfg)
+    assert mesh.size == 8 and sh.tiles_per_device == 3
+    with pytest.raises(ValueError, match="unknown key"):
+        config.load_config({"parallelization": {"tile_per_edge": 2}})
+    f = tmp_path / "config.yaml"
+    f.write_text("parallelization:\n  tiles_per_edge: 1\n  num_devices: 3\n  device_type: 'cpu'\nsolver:\n  N: 96\n")
+    cfg = config.load_config(f)
+    assert cfg["parallelization"]["num_devices"] == 3 and cfg["solver"]["N"] == 96 and cfg["solver"]["halo"] == 2

@@ -22,8 +22,8 @@ for N, p, overlap in ((48, 2 if world > 3 else 1, True), (96, 2, True), (96, 2, 
     if (6 * p * p) % world:
         continue
     g, steps = 2, 10
-    case = cases.make_case("tc2", N, alpha0=0.6)
-    par = orc.Params(N, g, axis=case.axis)
+    case = cases.make_case("tc5", N) if N == 96 else cases.make_case("tc2", N, alpha0=0.6)
+    par = orc.Params(N, g, axis=case.axis, hs=case.hs)
     ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
     st = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis, device=local, rank=rank,
                                 world=world, tangents=orc.centre_tangents(N), overlap=overlap)
@@ -31,6 +31,8 @@ for N, p, overlap in ((48, 2 if world > 3 else 1, True), (96, 2, True), (96, 2, 
     n = N // p
     raw = [orc.faces_to_tiles(orc.pad(x, g), p, g)[b:b + c] for x in (case.h, case.u1, case.u2)]   # ghosts empty
     dev = [torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in raw]
+    if case.hs is not None:
+        st.set_topography(torch.from_numpy(np.ascontiguousarray(orc.faces_to_tiles(orc.pad(case.hs, g), p, g)[b:b + c])).cuda())
     st.halo_fill(*dev)
     dt = cases.stable_dt(case)
     m0 = st.diagnostics(*dev).cpu().numpy()
