@@ -219,17 +219,12 @@ int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
         Q.push = ctx->d_push;
         ctx->stage_pushed = true;   // the caller can skip the ghost-fill launch (corner blocks are not refreshed)
     }
-    const int occ = env_int("CS_MARCH_OCC", 0);
+    // fp32: four columns per thread (one 16-byte access per row and variable) when rows allow it, else two;
+    // fp64: two.  CS_MARCH_VEC=2 forces the two-column fp32 variant (tuning aid).
     if constexpr (sizeof(R) == 4) {
-        const int vec = env_int("CS_MARCH_VEC", 4);
-        if (vec == 4 && P.m % 4 == 0 && ((size_t)P.m * sizeof(R)) % 16 == 0) {
-            if (occ == 3) return launch_march<R, 4, LIM, 3>(ctx, Q, lo, hi, s);
-            return launch_march<R, 4, LIM, 2>(ctx, Q, lo, hi, s);
-        }
+        if (env_int("CS_MARCH_VEC", 4) == 4 && P.m % 4 == 0) return launch_march<R, 4, LIM, 2>(ctx, Q, lo, hi, s);
         return launch_march<R, 2, LIM, 4>(ctx, Q, lo, hi, s);
     } else {
-        if (env_int("CS_MARCH_VEC", 2) == 1) return launch_march<R, 1, LIM, 4>(ctx, Q, lo, hi, s);
-        if (occ == 3) return launch_march<R, 2, LIM, 3>(ctx, Q, lo, hi, s);
         return launch_march<R, 2, LIM, 2>(ctx, Q, lo, hi, s);
     }
 }
