@@ -32,7 +32,7 @@ import numpy as np
 
 from . import _binding as B
 from . import topology
-from .topology import apply_operations, create_communication_schedule  # noqa: F401  (re-export)
+from .topology import apply_operations, create_communication_schedule, create_tile_schedule  # noqa: F401  (re-export)
 
 try:  # torch is plumbing (device memory, streams); host-only helpers work without it
     import torch

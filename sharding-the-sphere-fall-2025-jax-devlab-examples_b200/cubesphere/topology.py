@@ -116,6 +116,85 @@ def create_communication_schedule():
     return tuple(schedule)
 
 
+def create_tile_schedule(tiles_per_edge: int = 1):
+    """Edge-coloured exchange schedule for 6 p^2 tiles: the "scalable edge coloring" generalisation the
+    reference names but does not ship (deck slide 9; JAX-DevLab-Examples.py:31-37 raises for p != 1).
+
+    Returns a tuple of stages; each stage is a tuple of ``((tile_a, edge_a), (tile_b, edge_b), ops)``
+    entries in which no tile appears twice, and every one of the 12 p^2 tile-edge pairs (seams and
+    interior edges) appears exactly once.  ``ops`` is 'N' inside a face and the seam flag otherwise.
+    For p = 1 the result is :func:`create_communication_schedule` (the reference's own 4 stages).
+    The tile graph is 4-regular; colouring is greedy over a fixed edge order with repair by Kempe-chain
+    swaps, so it uses 4 stages whenever the greedy pass does and never more than 5 (Vizing).
+    The B200 halo kernels do not need the schedule (each ghost cell has a single writer); it exists for
+    callers that exchange by pairwise swaps like the reference does.
+    """
+    p = int(tiles_per_edge)
+    if p < 1:
+        raise ValueError(f"Error: tiles_per_edge = {p} must be >= 1.")
+    if p == 1:
+        return create_communication_schedule()
+    desc = edge_push_descriptors(p)
+    pairs = []
+    seen = set()
+    for t in range(num_tiles(p)):
+        face, ty, tx = tile_coords(t, p)
+        for e, name in enumerate(EDGES):
+            dt_, de = int(desc[t, e, 0]), int(desc[t, e, 1])
+            key = frozenset(((t, e), (dt_, de)))
+            if key in seen:
+                continue
+            seen.add(key)
+            inside = {"N": ty < p - 1, "S": ty > 0, "E": tx < p - 1, "W": tx > 0}[name]
+            pairs.append(((t, name), (dt_, EDGES[de]), "N" if inside else seam_op(face, name)))
+    colour = {}
+    used = {t: {} for t in range(num_tiles(p))}          # tile -> {colour: pair index}
+    ncol = 4
+
+    def free(t):
+        return [c for c in range(ncol) if c not in used[t]]
+
+    for k, ((ta, _), (tb, _), _) in enumerate(pairs):
+        while True:
+            common = [c for c in free(ta) if c in free(tb)]
+            if common:
+                c = common[0]
+                break
+            fa, fb = free(ta), free(tb)
+            if not fa or not fb:
+                ncol += 1
+                continue
+            # Kempe chain from tb alternating colours (ca, cb): swap them so that ca becomes free at tb
+            ca, cb = fa[0], fb[0]
+            chain, node, want = [], tb, ca
+            while want in used[node]:
+                j = used[node][want]
+                chain.append(j)
+                (x, _), (y, _), _ = pairs[j]
+                node = y if x == node else x
+                want = cb if want == ca else ca
+            if node == ta:                                 # the chain ends at ta: swapping would not help
+                ncol += 1
+                continue
+            for j in chain:
+                (x, _), (y, _), _ = pairs[j]
+                old = colour[j]
+                del used[x][old], used[y][old]
+            for j in chain:
+                (x, _), (y, _), _ = pairs[j]
+                new = cb if colour[j] == ca else ca
+                colour[j] = new
+                used[x][new] = j
+                used[y][new] = j
+        colour[k] = c
+        used[ta][c] = k
+        used[tb][c] = k
+    stages = [[] for _ in range(ncol)]
+    for k, pr in enumerate(pairs):
+        stages[colour[k]].append(pr)
+    return tuple(tuple(st) for st in stages if st)
+
+
 def apply_operations(data, operations: str):
     """Reverse the along-edge axis (last axis) for 'R'/'TR'; identity for 'N'/'T'.
 

@@ -404,3 +404,11 @@ def test_config_galewsky_c1536_against_oracle(built_library):
     errs32, _, _, _ = _run_case_c_oracle("galewsky", 1536, 5, dtype=np.float32)
     print("C1536 fp32 vs fp64 oracle after 5 steps, rel L2 (h, u, v):", errs32)
     assert errs32[0] <= 2e-5, errs32
+
+
+@pytest.mark.parametrize("N,dtype,tol", [(30, np.float32, 2e-5), (30, np.float64, 1e-13), (25, np.float64, 1e-13), (50, np.float32, 2e-5)])
+def test_awkward_row_lengths(built_library, N, dtype, tol):
+    """Row lengths that rule out the 16-byte fp32 path (N + 4 not a multiple of 4 -> two columns per thread)
+    or any vector path (odd N -> the one-thread-per-cell kernel): same answers as the oracle."""
+    r = _run_case("tc5", N, 6, dtype=dtype)
+    assert r["errs"][0] <= tol and r["errs"][1] <= 50 * tol and r["errs"][2] <= 50 * tol, r["errs"]

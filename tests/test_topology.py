@@ -161,3 +161,20 @@ def test_load_config_defaults_and_validation(tmp_path):
     f.write_text("parallelization:\n  tiles_per_edge: 1\n  num_devices: 3\n  device_type: 'cpu'\nsolver:\n  N: 96\n")
     cfg = config.load_config(f)
     assert cfg["parallelization"]["num_devices"] == 3 and cfg["solver"]["N"] == 96 and cfg["solver"]["halo"] == 2
+
+
+@pytest.mark.parametrize("p", [1, 2, 3, 4])
+def test_tile_schedule_is_a_proper_edge_colouring(p):
+    sched = topology.create_tile_schedule(p)
+    if p == 1:
+        assert sched == REFERENCE_SCHEDULE
+    assert len(sched) <= 5
+    seen = set()
+    for stage in sched:
+        tiles = [t for (ta, _), (tb, _), _ in stage for t in (ta, tb)]
+        assert len(tiles) == len(set(tiles))                       # no tile twice in a stage
+        for (ta, ea), (tb, eb), ops in stage:
+            key = frozenset(((ta, ea), (tb, eb)))
+            assert key not in seen and ops in ("N", "T", "R", "TR")
+            seen.add(key)
+    assert len(seen) == 12 * p * p                                  # every tile edge pair exactly once
