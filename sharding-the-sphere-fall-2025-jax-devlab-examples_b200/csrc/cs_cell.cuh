@@ -56,9 +56,9 @@ template <> CS_HD double cs_rsqrt<double>(double x) {
 }
 
 CS_HD float cs_min(float a, float b) { return fminf(a, b); }
-CS_HD double cs_min(double a, double b) { return fmin(a, b); }
+CS_HD double cs_min(double a, double b) { return a < b ? a : b; }   // no NaN handling needed: cheaper than fmin in fp64
 CS_HD float cs_max(float a, float b) { return fmaxf(a, b); }
-CS_HD double cs_max(double a, double b) { return fmax(a, b); }
+CS_HD double cs_max(double a, double b) { return a > b ? a : b; }
 CS_HD float cs_abs(float a) { return fabsf(a); }
 CS_HD double cs_abs(double a) { return fabs(a); }
 

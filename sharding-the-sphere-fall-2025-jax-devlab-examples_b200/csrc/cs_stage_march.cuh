@@ -81,6 +81,19 @@ __device__ __forceinline__ R march_half_slope(R dm, R dp) {
     const R c = R(0.25) * (dm + dp);
     return cs_max(R(0), cs_min(cs_min(dm, dp), c)) + cs_min(R(0), cs_max(cs_max(dm, dp), c));
 }
+// fp64 has no min / max instruction (each is a compare and two selects), so the double version takes the
+// minimum of the magnitudes and restores the common sign: same values, two thirds of the instructions.
+template <>
+__device__ __forceinline__ double march_half_slope<double, CS_LIM_MC>(double dm, double dp) {
+    const double c = 0.25 * (dm + dp);
+    const double mag = cs_min(cs_min(fabs(dm), fabs(dp)), fabs(c));
+    return dm * dp > 0.0 ? copysign(mag, dm) : 0.0;
+}
+template <>
+__device__ __forceinline__ double march_half_slope<double, CS_LIM_MINMOD>(double dm, double dp) {
+    const double mag = 0.5 * cs_min(fabs(dm), fabs(dp));
+    return dm * dp > 0.0 ? copysign(mag, dm) : 0.0;
+}
 
 // Four times the upwind face flux (the factor 1/4 is folded into MarchConst::kisg);
 // hsL, hsR are half slopes.
