@@ -34,6 +34,7 @@ extern "C" int cs_set_topography(cs_ctx* ctx, const void* hs, void* stream) {
     if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_set_topography: NULL context");
     CS_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
+    cs_drop_graphs(ctx);
     if (!hs) {
         ctx->has_topo = false;
         return CS_OK;

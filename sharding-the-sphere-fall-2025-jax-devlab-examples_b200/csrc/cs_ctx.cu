@@ -19,6 +19,14 @@ int cs_fail(const cs_ctx* ctx, int code, const char* fmt, ...) {
     return code;
 }
 
+void cs_drop_graphs(cs_ctx* ctx) {
+    for (StepGraph& g : ctx->graphs)
+        if (g.exec) {
+            cudaGraphExecDestroy(g.exec);
+            g = StepGraph();
+        }
+}
+
 extern "C" int cs_abi_version(void) { return CS_ABI_VERSION; }
 
 extern "C" const char* cs_last_error(const cs_ctx* ctx) { return ctx ? ctx->err.c_str() : g_thread_error.c_str(); }
@@ -169,8 +177,7 @@ extern "C" int cs_ctx_destroy(cs_ctx* ctx) {
     if (!ctx) return CS_OK;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
-    for (StepGraph& g : ctx->graphs)
-        if (g.exec) cudaGraphExecDestroy(g.exec);
+    cs_drop_graphs(ctx);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
     void* ptrs[] = {ctx->d_xt, ctx->d_ainv, ctx->d_xt64, ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, ctx->d_rot, ctx->d_push,
                     ctx->d_send_src, ctx->d_recv_dst, ctx->d_recv_code, ctx->d_send_off, ctx->d_recv_off, ctx->qa[0], ctx->qa[1], ctx->qa[2],

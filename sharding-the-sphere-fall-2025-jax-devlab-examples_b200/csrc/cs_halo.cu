@@ -152,6 +152,7 @@ extern "C" int cs_halo_set_rotation(cs_ctx* ctx, const double* rot, size_t n_gho
     if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_halo_set_rotation: NULL context");
     CS_CUDA(ctx, cudaSetDevice(ctx->device));
     CS_CUDA(ctx, cudaDeviceSynchronize());
+    cs_drop_graphs(ctx);
     if (ctx->d_rot) cudaFree(ctx->d_rot), ctx->d_rot = nullptr;
     if (!rot) return CS_OK;
     if (n_ghost != (size_t)ctx->n_local)

@@ -96,6 +96,7 @@ struct cs_ctx {
 };
 
 int cs_fail(const cs_ctx* ctx, int code, const char* fmt, ...);
+void cs_drop_graphs(cs_ctx* ctx);   // captured steps bake kernel arguments in: drop them when those change
 
 #define CS_CUDA(ctx, expr)                                                                       \
     do {                                                                                         \

@@ -412,3 +412,42 @@ def test_awkward_row_lengths(built_library, N, dtype, tol):
     or any vector path (odd N -> the one-thread-per-cell kernel): same answers as the oracle."""
     r = _run_case("tc5", N, 6, dtype=dtype)
     assert r["errs"][0] <= tol and r["errs"][1] <= 50 * tol and r["errs"][2] <= 50 * tol, r["errs"]
+
+
+def test_streams_graph_cache_and_two_contexts(built_library):
+    """cs_step replays cached CUDA graphs keyed by (arrays, dt): stepping on a side stream, alternating dt,
+    changing the topography and interleaving two contexts must all give the oracle's answer."""
+    N, g = 32, 2
+    case = cases.make_case("tc5", N)
+    par = orc.Params(N, g, axis=case.axis, hs=case.hs)
+    ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
+    hs = torch.from_numpy(par.hs).cuda()
+    ctxs = [api.Context(N, halo=g, axis=case.axis, tangents=orc.centre_tangents(N)) for _ in range(2)]
+    states = [[torch.from_numpy(x).cuda() for x in ref] for _ in range(2)]
+    for c in ctxs:
+        c.set_topography(hs)
+    dt = cases.stable_dt(case)
+    side = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    dts = [dt, 0.5 * dt, dt, 0.25 * dt, 0.5 * dt, dt, 0.7 * dt, 0.3 * dt]       # more distinct keys than cache slots
+    with torch.cuda.stream(side):
+        for d in dts:
+            for c, st in zip(ctxs, states):
+                c.step(*st, d)
+    side.synchronize()
+    for d in dts:
+        ref = orc.step(par, ref, d)
+    c_ = slice(g, g + N)
+    for st in states:
+        err = np.linalg.norm(st[0].cpu().numpy()[:, c_, c_] - ref[0][:, c_, c_]) / np.linalg.norm(ref[0][:, c_, c_])
+        assert err <= 1e-13, err
+    # dropping the topography invalidates the captured graphs (their kernels had the pointer baked in)
+    ctxs[0].set_topography(None)
+    flat = orc.Params(N, g, axis=case.axis)
+    ref2 = [x.copy() for x in ref]
+    ctxs[0].step(*states[0], dt)
+    ref2 = orc.step(flat, ref2, dt)
+    err = np.linalg.norm(states[0][0].cpu().numpy()[:, c_, c_] - ref2[0][:, c_, c_]) / np.linalg.norm(ref2[0][:, c_, c_])
+    assert err <= 1e-13, err
+    for c in ctxs:
+        c.close()
