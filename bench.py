@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--N", type=int, default=0, help="cells per face edge (default: weak-scaling table)")
+    ap.add_argument("--N", type=int, default=0, help="cells per face edge; fixes the sphere (strong scaling) instead of the weak-scaling table")
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--case", default="galewsky")
     ap.add_argument("--kernel", default="auto")
@@ -382,7 +382,7 @@ def run_ours(args):
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if args.N else "weak", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": f"{args.case} C{N}, SSP-RK3 (3 fused stages + halo) per step, {args.dtype}",
                        "N": N, "tiles_per_edge": p, "halo": g, "tiles_per_gpu": tc, "parallelism": f"tiles/{world}",
