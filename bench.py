@@ -302,15 +302,24 @@ def run_ours(args):
     # ---- halo: the ghost-fill launch alone, and what the step pays beyond its three stage kernels -------
     halo = None
     if world == 1:
+        # 50 fills captured in one CUDA graph: the replay time is device time, not host launch rate
         hev0, hev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        for _ in range(5):
+        for _ in range(3):
             stepper.ctx.halo_fill_state(*dev)
+        torch.cuda.synchronize()
+        hgraph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(hgraph):
+            for _ in range(50):
+                stepper.ctx.halo_fill_state(*dev)
+        hgraph.replay()
+        torch.cuda.synchronize()
         hev0.record()
-        for _ in range(100):
-            stepper.ctx.halo_fill_state(*dev)
+        for _ in range(4):
+            hgraph.replay()
         hev1.record()
         torch.cuda.synchronize()
-        fill_us = hev0.elapsed_time(hev1) * 1e3 / 100
+        fill_us = hev0.elapsed_time(hev1) * 1e3 / 200
+        del hgraph
         halo = {"fill_us": fill_us, "fills_per_step": len(roof["ms"]), "halo_us_per_step": fill_us * len(roof["ms"]),
                 "exposed_us_per_step": max(0.0, (ms / args.steps - sum(roof["ms"])) * 1e3)}
 

@@ -135,9 +135,9 @@ MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m,
     const int sms = ctx->num_sms - reserve > 8 ? ctx->num_sms - reserve : ctx->num_sms;
     const long long slots = (long long)sms * blocks_per_sm * (CS_MARCH_THREADS / 32);
     const int span = hi - lo;
-    int best_rows = span < 8 ? span : 8;
+    int best_rows = span < 4 ? span : 4;
     double best_cost = 1e300;
-    for (int rows = 8; rows <= 256 && rows <= span + 7; rows += 4) {
+    for (int rows = 4; rows <= 256 && rows <= span + 3; rows += 4) {
         const int r = rows < span ? rows : span;
         const long long items = (long long)G.nchunks * ((span + r - 1) / r) * T;
         const long long waves = (items + slots - 1) / slots;
