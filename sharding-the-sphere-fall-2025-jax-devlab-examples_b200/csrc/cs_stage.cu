@@ -6,6 +6,7 @@
 
 #include <cstdlib>
 #include <map>
+#include <mutex>
 #include <utility>
 
 namespace {
@@ -118,6 +119,8 @@ MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m,
     const int grp_last = (hi - 1 + g) / V;
     G.nchunks = (grp_last - G.grp0 + 1 + CS_MARCH_OUT_LANES - 1) / CS_MARCH_OUT_LANES;
     static std::map<std::pair<const void*, size_t>, int> occupancy;      // per kernel instantiation and smem size
+    static std::mutex occupancy_mutex;                                      // contexts may be driven from several host threads
+    std::lock_guard<std::mutex> lock(occupancy_mutex);
     const auto key = std::make_pair(reinterpret_cast<const void*>(kernel), smem);
     auto it = occupancy.find(key);
     if (it == occupancy.end()) {
@@ -173,6 +176,8 @@ int launch_tma(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_
     const int narr = 3 + (P.a != R(0) ? 3 : 0) + (P.topo ? 1 : 0);
     const size_t smem = (size_t)warps * ((size_t)ring * narr * cs_tma_astride<R, V>() + CS_TMA_MAX_RING * 8);
     static size_t configured = 0;     // per instantiation
+    static std::mutex configured_mutex;
+    std::lock_guard<std::mutex> lock(configured_mutex);
     if (smem > configured) {
         CS_CUDA(ctx, cudaFuncSetAttribute(stage_tma_kernel<R, V, LIM, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
