@@ -121,7 +121,8 @@ CS_API int cs_ctx_destroy(cs_ctx* ctx);
  * exchange_edge_pair (PY:166-197) incl. extract_boundary_data / apply_operations
  * / set_ghost_data (PY:143-163,184-195); ghost corners, which the reference never
  * writes, get the rule of DESIGN.md section 2.4.
- * Requires tile_count == 6 p^2 (single-device context); see cs_halo_pack for shards.
+ * On a sharded context (tile_count < 6 p^2) only the ghosts whose source tile is owned by the same
+ * context are filled; the others come through cs_halo_pack / cs_halo_unpack.
  */
 CS_API int cs_halo_fill_scalar(cs_ctx* ctx, void* field, void* stream);
 
