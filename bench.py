@@ -381,10 +381,12 @@ def run_ours(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            nsample = 3
-            val, threads, sec = cpu_run(case, dt, nsample, 1)
+            # about 15 s of CPU work: time one probe step, then size the sample
+            _, _, probe = cpu_run(case, dt, 1, 1)
+            nsample = int(max(3, min(300, 15.0 / max(probe, 1e-3))))
+            val, threads, sec = cpu_run(case, dt, nsample, 0)
             cpu = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                   "sample": f"{nsample} full fp64 steps of {args.case} C{N} after 1 warm-up, C + OpenMP oracle ({sec:.1f} s)"}
+                   "sample": f"{nsample} full fp64 steps of {args.case} C{N} after a warm-up, C + OpenMP oracle ({sec:.1f} s)"}
         except Exception as exc:  # pragma: no cover
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {exc}"}
 
