@@ -178,3 +178,15 @@ def test_tile_schedule_is_a_proper_edge_colouring(p):
             assert key not in seen and ops in ("N", "T", "R", "TR")
             seen.add(key)
     assert len(seen) == 12 * p * p                                  # every tile edge pair exactly once
+
+
+def test_state_files_round_trip(tmp_path):
+    from cubesphere import io
+    rng = np.random.default_rng(0)
+    state = {k: rng.standard_normal((24, 10, 10)).astype(np.float32) for k in ("h", "u", "v")}
+    f = io.save_state(tmp_path / "hist" / "s0001.npz", state, N=12, tiles_per_edge=2, halo=2, step=7, time=123.5, case="tc2")
+    got, meta = io.load_state(f)
+    assert all(np.array_equal(got[k], state[k]) for k in state)
+    assert (meta["N"], meta["tiles_per_edge"], meta["halo"], meta["step"], meta["time"], meta["case"]) == (12, 2, 2, 7, 123.5, "tc2")
+    with pytest.raises(ValueError):
+        io.save_state(tmp_path / "bad.npz", state, N=16, halo=2)
