@@ -72,7 +72,10 @@ StageParams<R> make_params(cs_ctx* ctx, const void* const q0[3], const void* con
     P.n = ctx->n, P.g = ctx->g, P.m = ctx->m, P.p = ctx->p, P.T = ctx->T, P.t0 = ctx->t0;
     P.part = part;
     P.advect_only = ctx->cfg.advect_only;
-    P.a = (R)a, P.b = (R)b, P.dt = (R)dt;
+    // a convex pair (a + b == 1) must stay one after rounding to R, or every step leaks a + b - 1 of the
+    // mass (fp32: (float)(1/3) + (float)(2/3) = 1 + 6e-8); 1 - b is exact for b in [1/4, 1]
+    P.b = (R)b, P.dt = (R)dt;
+    P.a = (a != 0.0 && a + b > 1.0 - 1e-12 && a + b < 1.0 + 1e-12) ? R(1) - P.b : (R)a;
     P.rd = (R)(1.0 / ctx->delta);
     P.r2d = (R)(0.5 / ctx->delta);
     P.a2 = (R)(ctx->radius * ctx->radius);
