@@ -15,10 +15,6 @@
 
 #include "cs_cell.cuh"
 
-#ifndef CS_OPT
-#define CS_OPT 31
-#endif
-
 struct MarchGeom {
     int prefetch;             // L2 prefetch distance in rows (0 = none)
     int xlo, xhi, ylo, yhi;   // interior index ranges [lo, hi) to update
@@ -31,10 +27,6 @@ struct MarchGeom {
 };
 
 __device__ __forceinline__ void march_prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-// predicated form: no branch, so the row body stays one basic block for the instruction scheduler
-__device__ __forceinline__ void march_prefetch_l2_if(const void* p, int on) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %1, 0;\n\t@p prefetch.global.L2 [%0];\n\t}" ::"l"(p), "r"(on));
-}
 
 template <typename R, int V> struct VecIO;
 template <> struct VecIO<float, 2> {
@@ -84,16 +76,12 @@ struct RowDerived {
 // minmod(dm, dp, (dm + dp) / 4) is bit-identical to cs_slope(dm, dp) / 2.
 template <typename R, int LIM>
 __device__ __forceinline__ R march_half_slope(R dm, R dp) {
+    // max(0, lo) + min(0, hi) with lo <= hi is the median of (lo, 0, hi) = max(lo, min(hi, 0)): bit-identical,
+    // one addition fewer
     if (LIM == CS_LIM_NONE) return R(0.25) * (dm + dp);
-#if CS_OPT & 1
     if (LIM == CS_LIM_MINMOD) return R(0.5) * cs_max(cs_min(dm, dp), cs_min(cs_max(dm, dp), R(0)));
     const R c = R(0.25) * (dm + dp);
     return cs_max(cs_min(cs_min(dm, dp), c), cs_min(cs_max(cs_max(dm, dp), c), R(0)));
-#else
-    if (LIM == CS_LIM_MINMOD) return R(0.5) * (cs_max(R(0), cs_min(dm, dp)) + cs_min(R(0), cs_max(dm, dp)));
-    const R c = R(0.25) * (dm + dp);
-    return cs_max(R(0), cs_min(cs_min(dm, dp), c)) + cs_min(R(0), cs_max(cs_max(dm, dp), c));
-#endif
 }
 // fp64 has no min / max instruction (each is a compare and two selects), so the double version takes the
 // minimum of the magnitudes and restores the common sign: same values, two thirds of the instructions.
@@ -109,16 +97,13 @@ __device__ __forceinline__ double march_half_slope<double, CS_LIM_MINMOD>(double
     return dm * dp > 0.0 ? copysign(mag, dm) : 0.0;
 }
 
-// Four times the upwind face flux (the factor 1/4 is folded into MarchConst::kisg);
-// hsL, hsR are half slopes.
+// Four times the upwind face flux (the factor 1/4 is folded into MarchConst::kisg); hsL, hsR are half slopes.
+// 2 M (hL + hsL) for M > 0, 2 M (hR - hsR) otherwise: what the oracle's M (l + r) + |M| (l - r) evaluates to, up
+// to one rounding, with the compare and the select on the ALU pipe instead of two more FMA-pipe operations.
 template <typename R>
 __device__ __forceinline__ R march_flux4(R mL, R mR, R hL, R hsL, R hR, R hsR) {
     const R M = mL + mR, left = hL + hsL, right = hR - hsR;
-#if CS_OPT & 2
     return (M + M) * (M > R(0) ? left : right);
-#else
-    return M * (left + right) + cs_abs(M) * (left - right);
-#endif
 }
 
 // Constants folded once per thread so that the row loop multiplies as little as possible:
@@ -146,15 +131,9 @@ __device__ __forceinline__ void march_derive(const StageParams<R>& P, const Marc
         const R sg = cc * rho;
         D.m1[c] = sg * u[c];
         D.m2[c] = sg * v[c];
-#if CS_OPT & 4
         const R XY = K.X[c] * Y;
         D.c1[c] = cc * ((rho2 - Y2) * u[c] - XY * v[c]);
         D.c2[c] = cc * (B * v[c] - XY * u[c]);
-#else
-        const R g11 = cc * (rho2 - Y2), g22 = cc * B, g12 = -(cc * K.X[c]) * Y;     // 1 + X^2 = rho^2 - Y^2
-        D.c1[c] = g11 * u[c] + g12 * v[c];
-        D.c2[c] = g12 * u[c] + g22 * v[c];
-#endif
         const R Kin = R(0.5) * (u[c] * D.c1[c] + v[c] * D.c2[c]);
         D.Bn[c] = P.grav * (h[c] + hs[c]) + Kin;
         D.q[c] = rho2 * K.kq;
@@ -247,24 +226,14 @@ __device__ __forceinline__ void march_row_update(const StageParams<R>& P, const 
         oh[c] = P.b * hc[c] - ((F[c + 1] - F[c]) + dG[c]) * Dcur.isg[c];
         ou[c] = P.b * uc[c];
         ov[c] = P.b * vc[c];
-#if CS_OPT & 16
-        {   // advection only: kq == 0 switches the tendencies off without a branch per column
-#else
-        if (!P.advect_only) {
-#endif
+        {   // advection only: kq == 0 switches the tendencies off; a branch here would cut the row body into
+            // one basic block per column and keep the scheduler from interleaving the V dependency chains
             const R eta = ((c2e[c + 2] - c2e[c]) - (Dnext.c1[c] - c1m[c])) + Dcur.fsg[c];
             const R T1 = eta * vc[c] - (Bne[c + 2] - Bne[c]);
             const R T2 = -eta * uc[c] - (Dnext.Bn[c] - Bnm[c]);
-#if CS_OPT & 8
             const R w12 = K.Xax[c] * Yay;
             ou[c] += Dcur.q[c] * (K.ax[c] * T1 + w12 * T2);
             ov[c] += Dcur.q[c] * (w12 * T1 + ay * T2);
-#else
-            const R gi11 = Dcur.q[c] * K.ax[c], gi22 = Dcur.q[c] * ay;
-            const R gi12 = (Dcur.q[c] * K.Xax[c]) * Yay;
-            ou[c] += gi11 * T1 + gi12 * T2;
-            ov[c] += gi12 * T1 + gi22 * T2;
-#endif
         }
         if (read_q0) {
             oh[c] += P.a * q0h[c];
@@ -303,9 +272,7 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     {
         const R kf = P.two_omega / P.r2d;
         K.kq = P.ia2 * P.b * P.dt * P.r2d;
-#if CS_OPT & 16
         if (P.advect_only) K.kq = R(0);
-#endif
         K.kisg = R(0.25) * P.ia2 * P.b * P.dt * P.rd;   // 1/4: fluxes are carried times four
         K.kf2 = kf * cf[2];
 #pragma unroll
@@ -398,23 +365,7 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
         }
         // Pull the lines that will be loaded pf_rows rows from now into L2 (no registers involved): the
         // register prefetch above is one row deep, which covers an L2 hit but not a trip to HBM.
-#if CS_OPT & 32
-        {
-            const int on = pf_rows > 0 && pf_lane, onq = on && read_q0;
-            const unsigned op = tbase + (unsigned)min(J + 3 + pf_rows, m - 1) * m;
-            const unsigned oq = tbase + (unsigned)min(J + pf_rows, m - 1) * m;
-            march_prefetch_l2_if(P.hq + op, on);
-            march_prefetch_l2_if(P.uq + op, on);
-            march_prefetch_l2_if(P.vq + op, on);
-            march_prefetch_l2_if(P.topo + op, on && has_topo);
-            march_prefetch_l2_if(P.h0 + oq, onq);
-            march_prefetch_l2_if(P.u0 + oq, onq);
-            march_prefetch_l2_if(P.v0 + oq, onq);
-        }
-        if (false) {
-#else
         if (pf_rows > 0 && pf_lane) {
-#endif
             const unsigned op = tbase + (unsigned)min(J + 3 + pf_rows, m - 1) * m;
             march_prefetch_l2(P.hq + op);
             march_prefetch_l2(P.uq + op);
