@@ -10,7 +10,7 @@
  *   - every device pointer is caller-owned memory on the context's device;
  *   - every call only ENQUEUES work on the given stream (a cudaStream_t passed as
  *     void*; NULL = the legacy default stream) and never synchronises, except
- *     cs_ctx_create / cs_ctx_destroy / cs_step_host which own their synchronisation;
+ *     cs_ctx_create / cs_ctx_destroy / cs_step_host[_batch] which own their synchronisation;
  *   - return value 0 = success, negative = CS_E_* below; the text of the last
  *     error of a context (or of the calling thread when ctx is NULL) is
  *     cs_last_error();
@@ -200,6 +200,20 @@ CS_API int cs_diagnostics(cs_ctx* ctx, const void* h, const void* u, const void*
  */
 CS_API int cs_step_host(cs_ctx* ctx, void* h_host, void* u_host, void* v_host, double dt, int nsteps,
                  double* diag_host, int copy_back);
+
+/*
+ * The same for `members` independent host-resident states (an ensemble, or a
+ * batch of requests): member i is h_host[i], u_host[i], v_host[i]; its mass and
+ * energy go to diag_host[2 i .. 2 i + 1] (diag_host may be NULL).  The members
+ * stream through two device slots on three internal streams, so the upload of
+ * member i + 1 and the download of member i - 1 overlap the steps of member i;
+ * use page-locked host memory or the copies serialise.  Results are those of
+ * `members` cs_step_host calls.  Synchronises.  No counterpart in the reference
+ * (its states live on the devices, PY:174); this is the host-array form of
+ * step(state, dt) for more states than fit in, or are wanted on, the GPU.
+ */
+CS_API int cs_step_host_batch(cs_ctx* ctx, int members, void* const* h_host, void* const* u_host, void* const* v_host,
+                       double dt, int nsteps, double* diag_host, int copy_back);
 
 /*
  * Sharded halo exchange (tile_count < 6 p^2).  The context splits its ghost

@@ -211,3 +211,85 @@ extern "C" int cs_step_host(cs_ctx* ctx, void* h_host, void* u_host, void* v_hos
     if (e != cudaSuccess) return cs_fail(ctx, CS_E_CUDA, "cs_step_host: %s", cudaGetErrorString(e));
     return CS_OK;
 }
+
+namespace {
+
+// Streams, events and the second device slot of cs_step_host_batch, created on first use.
+int pipe_setup(cs_ctx* ctx) {
+    cs_ctx::HostPipe& p = ctx->pipe;
+    const size_t bytes = ctx->field_elems * ctx->esize;
+    for (int k = 0; k < 3; ++k) {
+        if (!ctx->host_state[k] && cudaMalloc(&ctx->host_state[k], bytes) != cudaSuccess)
+            return cs_fail(ctx, CS_E_NOMEM, "cs_step_host_batch: cudaMalloc of %zu bytes failed", bytes);
+        p.state[0][k] = ctx->host_state[k];
+        if (!p.state[1][k] && cudaMalloc(&p.state[1][k], bytes) != cudaSuccess)
+            return cs_fail(ctx, CS_E_NOMEM, "cs_step_host_batch: cudaMalloc of %zu bytes failed", bytes);
+    }
+    if (p.ready) return CS_OK;
+    if (cudaMalloc((void**)&p.diag, 4 * sizeof(double)) != cudaSuccess)
+        return cs_fail(ctx, CS_E_NOMEM, "cs_step_host_batch: cudaMalloc failed");
+    for (cudaStream_t* s : {&p.in, &p.compute, &p.out})
+        CS_CUDA(ctx, cudaStreamCreateWithFlags(s, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; ++k)
+        for (cudaEvent_t* e : {&p.in_done[k], &p.compute_done[k], &p.out_done[k]})
+            CS_CUDA(ctx, cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    p.ready = true;
+    return CS_OK;
+}
+
+}  // namespace
+
+extern "C" int cs_step_host_batch(cs_ctx* ctx, int members, void* const* h_host, void* const* u_host, void* const* v_host,
+                                  double dt, int nsteps, double* diag_host, int copy_back) {
+    if (!ctx || !h_host || !u_host || !v_host) return cs_fail(ctx, CS_E_INVALID, "cs_step_host_batch: NULL argument");
+    if (members < 0 || nsteps < 0)
+        return cs_fail(ctx, CS_E_INVALID, "cs_step_host_batch: members = %d and nsteps = %d must be >= 0", members, nsteps);
+    for (int i = 0; i < members; ++i)
+        if (!h_host[i] || !u_host[i] || !v_host[i]) return cs_fail(ctx, CS_E_INVALID, "cs_step_host_batch: member %d has a NULL array", i);
+    int rc = check_step_ready(ctx, "cs_step_host_batch");
+    if (rc) return rc;
+    if (!single_device(ctx)) return cs_fail(ctx, CS_E_INVALID, "cs_step_host_batch needs a context that owns all tiles");
+    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_CUDA(ctx, cudaDeviceSynchronize());                // earlier work on other streams may still use the slots
+    if ((rc = pipe_setup(ctx))) return rc;
+    cs_ctx::HostPipe& p = ctx->pipe;
+    const size_t bytes = ctx->field_elems * ctx->esize;
+    auto drain = [&](int code) {
+        cudaStreamSynchronize(p.in), cudaStreamSynchronize(p.compute), cudaStreamSynchronize(p.out);
+        return code;
+    };
+#define CS_PIPE(call)                                                                                       \
+    do {                                                                                                    \
+        cudaError_t e_ = (call);                                                                            \
+        if (e_ != cudaSuccess) return drain(cs_fail(ctx, CS_E_CUDA, "cs_step_host_batch: %s", cudaGetErrorString(e_))); \
+    } while (0)
+    for (int i = 0; i < members; ++i) {
+        const int k = i & 1;
+        void* const hostp[3] = {h_host[i], u_host[i], v_host[i]};
+        void** d = p.state[k];
+        // upload: the slot is free once member i - 2 has been stepped (and, with copy_back, downloaded)
+        if (i >= 2) CS_PIPE(cudaStreamWaitEvent(p.in, copy_back ? p.out_done[k] : p.compute_done[k], 0));
+        for (int c = 0; c < 3; ++c) CS_PIPE(cudaMemcpyAsync(d[c], hostp[c], bytes, cudaMemcpyHostToDevice, p.in));
+        CS_PIPE(cudaEventRecord(p.in_done[k], p.in));
+        // steps (members share the context's scratch, so they run one after the other on one stream)
+        CS_PIPE(cudaStreamWaitEvent(p.compute, p.in_done[k], 0));
+        if (i >= 2) CS_PIPE(cudaStreamWaitEvent(p.compute, p.out_done[k], 0));      // its diagnostics slot has been read
+        if ((rc = cs_launch_halo(ctx, d[0], d[1], d[2], 3, p.compute))) return drain(rc);
+        for (int it = 0; it < nsteps; ++it)
+            if ((rc = cs_step(ctx, d[0], d[1], d[2], dt, nullptr, p.compute))) return drain(rc);
+        if (diag_host && (rc = cs_launch_diag(ctx, d[0], d[1], d[2], p.diag + 2 * k, p.compute))) return drain(rc);
+        CS_PIPE(cudaEventRecord(p.compute_done[k], p.compute));
+        // download
+        CS_PIPE(cudaStreamWaitEvent(p.out, p.compute_done[k], 0));
+        if (diag_host) CS_PIPE(cudaMemcpyAsync(diag_host + 2 * i, p.diag + 2 * k, 2 * sizeof(double), cudaMemcpyDeviceToHost, p.out));
+        if (copy_back)
+            for (int c = 0; c < 3; ++c) CS_PIPE(cudaMemcpyAsync(hostp[c], d[c], bytes, cudaMemcpyDeviceToHost, p.out));
+        CS_PIPE(cudaEventRecord(p.out_done[k], p.out));
+    }
+#undef CS_PIPE
+    cudaError_t e = cudaStreamSynchronize(p.out);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p.compute);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p.in);
+    if (e != cudaSuccess) return cs_fail(ctx, CS_E_CUDA, "cs_step_host_batch: %s", cudaGetErrorString(e));
+    return CS_OK;
+}

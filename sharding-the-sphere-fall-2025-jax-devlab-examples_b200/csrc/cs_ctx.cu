@@ -179,6 +179,14 @@ extern "C" int cs_ctx_destroy(cs_ctx* ctx) {
     cudaDeviceSynchronize();
     cs_drop_graphs(ctx);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
+    for (cudaStream_t s : {ctx->pipe.in, ctx->pipe.compute, ctx->pipe.out})
+        if (s) cudaStreamDestroy(s);
+    for (int k = 0; k < 2; ++k)
+        for (cudaEvent_t e : {ctx->pipe.in_done[k], ctx->pipe.compute_done[k], ctx->pipe.out_done[k]})
+            if (e) cudaEventDestroy(e);
+    for (int k = 0; k < 3; ++k)
+        if (ctx->pipe.state[1][k]) cudaFree(ctx->pipe.state[1][k]);
+    if (ctx->pipe.diag) cudaFree(ctx->pipe.diag);
     void* ptrs[] = {ctx->d_xt, ctx->d_ainv, ctx->d_xt64, ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, ctx->d_rot, ctx->d_push,
                     ctx->d_send_src, ctx->d_recv_dst, ctx->d_recv_code, ctx->d_send_off, ctx->d_recv_off, ctx->qa[0], ctx->qa[1], ctx->qa[2],
                     ctx->qb[0], ctx->qb[1], ctx->qb[2], ctx->topo, ctx->host_state[0], ctx->host_state[1], ctx->host_state[2], ctx->d_partials, ctx->d_diag, ctx->d_ticket};

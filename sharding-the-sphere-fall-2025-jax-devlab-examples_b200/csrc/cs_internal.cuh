@@ -79,6 +79,13 @@ struct cs_ctx {
     void* qb[3] = {nullptr, nullptr, nullptr};
     void* topo = nullptr;
     void* host_state[3] = {nullptr, nullptr, nullptr};   // device copy used by cs_step_host
+    struct HostPipe {                                     // cs_step_host_batch: two device slots, three streams
+        bool ready = false;
+        void* state[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};   // slot 0 aliases host_state
+        double* diag = nullptr;                           // [2][2]
+        cudaStream_t in = nullptr, compute = nullptr, out = nullptr;
+        cudaEvent_t in_done[2] = {nullptr, nullptr}, compute_done[2] = {nullptr, nullptr}, out_done[2] = {nullptr, nullptr};
+    } pipe;
     bool has_topo = false;
 
     // reductions

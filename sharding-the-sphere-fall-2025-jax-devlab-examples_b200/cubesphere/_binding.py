@@ -50,6 +50,8 @@ _PROTOTYPES = {
     "cs_step": (C.c_int, [_VP, _VP, _VP, _VP, C.c_double, _VP, _VP]),
     "cs_diagnostics": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     "cs_step_host": (C.c_int, [_VP, _VP, _VP, _VP, C.c_double, C.c_int, C.POINTER(C.c_double), C.c_int]),
+    "cs_step_host_batch": (C.c_int, [_VP, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), C.c_double, C.c_int,
+                                     C.POINTER(C.c_double), C.c_int]),
     "cs_halo_plan": (C.c_int, [_VP, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "cs_halo_pack": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP, _VP]),

@@ -366,8 +366,7 @@ class Context:
                                              C.c_void_p(out.data_ptr()), self._stream()))
         return out
 
-    def step_host(self, h, u, v, dt, nsteps=1, copy_back=True, diag=True):
-        """Host-buffer entry: NumPy arrays (or pinned CPU tensors) in the padded layout, updated in place."""
+    def _host_ptrs(self, h, u, v):
         ptrs = []
         np_dtype = np.float64 if self.dtype is torch.float64 else np.float32
         for name, a in (("h", h), ("u", u), ("v", v)):
@@ -379,10 +378,27 @@ class Context:
                 if not isinstance(a, np.ndarray) or a.dtype != np_dtype or a.shape != self.shape or not a.flags.c_contiguous:
                     raise ValueError(f"{name}: need a C-contiguous array of shape {self.shape} and dtype {np_dtype.__name__}")
                 ptrs.append(C.c_void_p(a.ctypes.data))
+        return ptrs
+
+    def step_host(self, h, u, v, dt, nsteps=1, copy_back=True, diag=True):
+        """Host-buffer entry: NumPy arrays (or pinned CPU tensors) in the padded layout, updated in place."""
+        ptrs = self._host_ptrs(h, u, v)
         out = (C.c_double * 2)()
         self._check(self._lib.cs_step_host(self._h, ptrs[0], ptrs[1], ptrs[2], float(dt), int(nsteps),
                                            out if diag else None, int(bool(copy_back))))
         return (out[0], out[1]) if diag else None
+
+    def step_host_batch(self, members, dt, nsteps=1, copy_back=True, diag=True):
+        """``members``: sequence of (h, u, v) host states (an ensemble).  Uploads, steps and downloads overlap
+        across members (two device slots); page-locked arrays are needed for that.  Returns [members, 2]
+        mass / energy (or None)."""
+        M = len(members)
+        cols = list(zip(*(self._host_ptrs(*m) for m in members))) if M else [(), (), ()]
+        arrs = [(C.c_void_p * M)(*col) for col in cols]
+        out = (C.c_double * (2 * max(M, 1)))()
+        self._check(self._lib.cs_step_host_batch(self._h, M, arrs[0], arrs[1], arrs[2], float(dt), int(nsteps),
+                                                 out if diag else None, int(bool(copy_back))))
+        return np.array(out[:2 * M], dtype=np.float64).reshape(M, 2) if diag else None
 
     # -- sharded exchange -----------------------------------------------------
     def halo_plan(self, tile_begins, tile_counts):

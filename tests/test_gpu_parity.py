@@ -468,3 +468,37 @@ def test_fp32_mass_does_not_leak(built_library):
     m1 = ctx.diagnostics(*dev).cpu().numpy()[0]
     assert abs(m1 - m0) / m0 <= 2e-6, (m1 - m0) / m0          # was 1.2e-5 with the leak; round-off walk is ~1e-7
     ctx.close()
+
+
+@pytest.mark.parametrize("copy_back", [True, False])
+def test_step_host_batch_equals_single_calls(built_library, copy_back):
+    """Ensemble members streamed through two device slots (upload / steps / download overlapped) give exactly
+    what one cs_step_host call per member gives; the first member is also checked against the oracle."""
+    N, g, M = 48, 2, 5
+    case = cases.make_case("tc5", N)
+    par = orc.Params(N, g, axis=case.axis, hs=case.hs)
+    ctx = api.Context(N, halo=g, axis=case.axis, tangents=orc.centre_tangents(N))
+    ctx.set_topography(torch.from_numpy(par.hs).cuda())
+    dt = cases.stable_dt(case)
+    base = [orc.pad(x, g) for x in (case.h, case.u1, case.u2)]
+    members = [[torch.from_numpy(x * (1.0 + 0.01 * i)).pin_memory() for x in base] for i in range(M)]
+    singles = [[x.clone() for x in m] for m in members]
+    ref_diag = np.array([ctx.step_host(*(x.numpy() for x in s), dt, nsteps=3, copy_back=True) for s in singles])
+    diag = ctx.step_host_batch(members, dt, nsteps=3, copy_back=copy_back)
+    assert np.array_equal(diag, ref_diag)
+    c_ = slice(g, g + N)
+    for m, s, m0 in zip(members, singles, range(M)):
+        for a, b, x0 in zip(m, s, base):
+            if copy_back:
+                assert np.array_equal(a.numpy()[:, c_, c_], b.numpy()[:, c_, c_])
+            else:
+                assert np.array_equal(a.numpy(), x0 * (1.0 + 0.01 * m0))            # inputs untouched
+    ref = orc.halo_fill_state(*base, g)
+    for _ in range(3):
+        ref = orc.step(par, ref, dt)
+    err = np.linalg.norm(singles[0][0].numpy()[:, c_, c_] - ref[0][:, c_, c_]) / np.linalg.norm(ref[0][:, c_, c_])
+    assert err <= 1e-13, err
+    assert ctx.step_host_batch([], dt) .shape == (0, 2)
+    with pytest.raises(ValueError):
+        ctx.step_host_batch([members[0][:2] + [members[0][0][:, :-1]]], dt)
+    ctx.close()
