@@ -1,6 +1,8 @@
 // Entry points that compose the kernels: topography, one RK stage, one step, host-buffer step.
 #include <cstdlib>
 
+#include <cstring>
+
 #include "cs_internal.cuh"
 
 namespace {
@@ -254,6 +256,15 @@ extern "C" int cs_step_host_batch(cs_ctx* ctx, int members, void* const* h_host,
     if ((rc = pipe_setup(ctx))) return rc;
     cs_ctx::HostPipe& p = ctx->pipe;
     const size_t bytes = ctx->field_elems * ctx->esize;
+    // A device-to-host copy into pageable memory blocks the calling thread until it is done, which would keep the
+    // next member's upload from even being enqueued: the diagnostics go through a page-locked staging array.
+    if (diag_host && members > p.diag_cap) {
+        if (p.diag_pinned) cudaFreeHost(p.diag_pinned);
+        p.diag_pinned = nullptr, p.diag_cap = 0;
+        if (cudaHostAlloc((void**)&p.diag_pinned, (size_t)members * 2 * sizeof(double), cudaHostAllocDefault) != cudaSuccess)
+            return cs_fail(ctx, CS_E_NOMEM, "cs_step_host_batch: cudaHostAlloc failed");
+        p.diag_cap = members;
+    }
     auto drain = [&](int code) {
         cudaStreamSynchronize(p.in), cudaStreamSynchronize(p.compute), cudaStreamSynchronize(p.out);
         return code;
@@ -281,7 +292,7 @@ extern "C" int cs_step_host_batch(cs_ctx* ctx, int members, void* const* h_host,
         CS_PIPE(cudaEventRecord(p.compute_done[k], p.compute));
         // download
         CS_PIPE(cudaStreamWaitEvent(p.out, p.compute_done[k], 0));
-        if (diag_host) CS_PIPE(cudaMemcpyAsync(diag_host + 2 * i, p.diag + 2 * k, 2 * sizeof(double), cudaMemcpyDeviceToHost, p.out));
+        if (diag_host) CS_PIPE(cudaMemcpyAsync(p.diag_pinned + 2 * i, p.diag + 2 * k, 2 * sizeof(double), cudaMemcpyDeviceToHost, p.out));
         if (copy_back)
             for (int c = 0; c < 3; ++c) CS_PIPE(cudaMemcpyAsync(hostp[c], d[c], bytes, cudaMemcpyDeviceToHost, p.out));
         CS_PIPE(cudaEventRecord(p.out_done[k], p.out));
@@ -291,5 +302,6 @@ extern "C" int cs_step_host_batch(cs_ctx* ctx, int members, void* const* h_host,
     if (e == cudaSuccess) e = cudaStreamSynchronize(p.compute);
     if (e == cudaSuccess) e = cudaStreamSynchronize(p.in);
     if (e != cudaSuccess) return cs_fail(ctx, CS_E_CUDA, "cs_step_host_batch: %s", cudaGetErrorString(e));
+    if (diag_host && members > 0) std::memcpy(diag_host, p.diag_pinned, (size_t)members * 2 * sizeof(double));
     return CS_OK;
 }

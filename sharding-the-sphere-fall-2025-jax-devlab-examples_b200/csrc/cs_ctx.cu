@@ -187,6 +187,7 @@ extern "C" int cs_ctx_destroy(cs_ctx* ctx) {
     for (int k = 0; k < 3; ++k)
         if (ctx->pipe.state[1][k]) cudaFree(ctx->pipe.state[1][k]);
     if (ctx->pipe.diag) cudaFree(ctx->pipe.diag);
+    if (ctx->pipe.diag_pinned) cudaFreeHost(ctx->pipe.diag_pinned);
     void* ptrs[] = {ctx->d_xt, ctx->d_ainv, ctx->d_xt64, ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, ctx->d_rot, ctx->d_push,
                     ctx->d_send_src, ctx->d_recv_dst, ctx->d_recv_code, ctx->d_send_off, ctx->d_recv_off, ctx->qa[0], ctx->qa[1], ctx->qa[2],
                     ctx->qb[0], ctx->qb[1], ctx->qb[2], ctx->topo, ctx->host_state[0], ctx->host_state[1], ctx->host_state[2], ctx->d_partials, ctx->d_diag, ctx->d_ticket};

@@ -83,6 +83,8 @@ struct cs_ctx {
         bool ready = false;
         void* state[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};   // slot 0 aliases host_state
         double* diag = nullptr;                           // [2][2]
+        double* diag_pinned = nullptr;                    // page-locked staging for the members' [mass, energy]
+        int diag_cap = 0;                                 // ... in members
         cudaStream_t in = nullptr, compute = nullptr, out = nullptr;
         cudaEvent_t in_done[2] = {nullptr, nullptr}, compute_done[2] = {nullptr, nullptr}, out_done[2] = {nullptr, nullptr};
     } pipe;
