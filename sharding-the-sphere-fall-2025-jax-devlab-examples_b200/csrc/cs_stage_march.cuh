@@ -186,7 +186,7 @@ __device__ __forceinline__ void march_push_store(const StageParams<R>& P, const 
 // TMA-fed kernels).  Each lane computes the half slopes of its own V cells and the V faces on
 // their left; the neighbour's slope and the right-most face come by shuffle, so no slope or flux
 // is computed twice within a warp (and both sides of a face see one value).
-template <typename R, int V, int LIM>
+template <typename R, int V, int LIM, bool UNIT = false>
 __device__ __forceinline__ void march_row_update(const StageParams<R>& P, const MarchConst<R, V>& K,
                                                  const RowDerived<R, V>& Dcur, const RowDerived<R, V>& Dnext,
                                                  const R (&hc)[V], const R (&uc)[V], const R (&vc)[V], const R (&dG)[V],
@@ -223,9 +223,10 @@ __device__ __forceinline__ void march_row_update(const StageParams<R>& P, const 
 #pragma unroll
     for (int c = 0; c < V; ++c) {
         // every factor b, dt, 1/delta, 1/a^2 is already inside isg, q and fsg (MarchConst)
-        oh[c] = P.b * hc[c] - ((F[c + 1] - F[c]) + dG[c]) * Dcur.isg[c];
-        ou[c] = P.b * uc[c];
-        ov[c] = P.b * vc[c];
+        // UNIT: the first stage of every scheme, (a, b) = (0, 1) -- no q0, no multiplication by b
+        oh[c] = (UNIT ? hc[c] : P.b * hc[c]) - ((F[c + 1] - F[c]) + dG[c]) * Dcur.isg[c];
+        ou[c] = UNIT ? uc[c] : P.b * uc[c];
+        ov[c] = UNIT ? vc[c] : P.b * vc[c];
         {   // advection only: kq == 0 switches the tendencies off; a branch here would cut the row body into
             // one basic block per column and keep the scheduler from interleaving the V dependency chains
             const R eta = ((c2e[c + 2] - c2e[c]) - (Dnext.c1[c] - c1m[c])) + Dcur.fsg[c];
@@ -235,7 +236,7 @@ __device__ __forceinline__ void march_row_update(const StageParams<R>& P, const 
             ou[c] += Dcur.q[c] * (K.ax[c] * T1 + w12 * T2);
             ov[c] += Dcur.q[c] * (w12 * T1 + ay * T2);
         }
-        if (read_q0) {
+        if (!UNIT && read_q0) {
             oh[c] += P.a * q0h[c];
             ou[c] += P.a * q0u[c];
             ov[c] += P.a * q0v[c];
@@ -243,7 +244,7 @@ __device__ __forceinline__ void march_row_update(const StageParams<R>& P, const 
     }
 }
 
-template <typename R, int V, int LIM, int MINB, bool PUSH>
+template <typename R, int V, int LIM, int MINB, bool PUSH, bool UNIT = false>
 __global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
 stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant__ MarchGeom G) {
     const int lane = threadIdx.x & 31;
@@ -264,7 +265,7 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     const R* yt = P.xt + tc.ty * P.n;
     const R* ayt = P.ainv + tc.ty * P.n;
     const R* cf = P.cf[tc.face];
-    const bool has_topo = P.topo != nullptr, read_q0 = P.a != R(0);
+    const bool has_topo = P.topo != nullptr, read_q0 = !UNIT && P.a != R(0);
 
     MarchConst<R, V> K;
     bool om[V];
@@ -393,7 +394,7 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
         }
 
         R oh[V], ou[V], ov[V];
-        march_row_update<R, V, LIM>(P, K, Dcur, Dnext, hc, uc, vc, dG, c1m, Bnm, Yc, ayc, read_q0, q0h, q0u, q0v, oh, ou, ov);
+        march_row_update<R, V, LIM, UNIT>(P, K, Dcur, Dnext, hc, uc, vc, dG, c1m, Bnm, Yc, ayc, read_q0, q0h, q0u, q0v, oh, ou, ov);
         if (all_out) {
             IO::st(P.ho + oJ, oh);
             IO::st(P.uo + oJ, ou);
