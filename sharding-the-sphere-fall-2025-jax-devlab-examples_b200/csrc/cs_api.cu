@@ -261,9 +261,10 @@ extern "C" int cs_step_host_batch(cs_ctx* ctx, int members, void* const* h_host,
     if (diag_host && members > p.diag_cap) {
         if (p.diag_pinned) cudaFreeHost(p.diag_pinned);
         p.diag_pinned = nullptr, p.diag_cap = 0;
-        if (cudaHostAlloc((void**)&p.diag_pinned, (size_t)members * 2 * sizeof(double), cudaHostAllocDefault) != cudaSuccess)
+        const int cap = members < 1024 ? 1024 : members;   // page-locking is slow: do it once for any ordinary batch
+        if (cudaHostAlloc((void**)&p.diag_pinned, (size_t)cap * 2 * sizeof(double), cudaHostAllocDefault) != cudaSuccess)
             return cs_fail(ctx, CS_E_NOMEM, "cs_step_host_batch: cudaHostAlloc failed");
-        p.diag_cap = members;
+        p.diag_cap = cap;
     }
     auto drain = [&](int code) {
         cudaStreamSynchronize(p.in), cudaStreamSynchronize(p.compute), cudaStreamSynchronize(p.out);
