@@ -165,7 +165,12 @@ extern "C" int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double
     if (cudaStreamIsCapturing(s, &cap) != cudaSuccess) cudaGetLastError(), cap = cudaStreamCaptureStatusNone;
     static const bool want_graph = []() { const char* e = std::getenv("CS_STEP_GRAPH"); return !(e && *e == '0'); }();
     if (want_graph && cap == cudaStreamCaptureStatusNone) {
-        if (StepGraph* g = find_or_capture(ctx, h, u, v, dt, diag_out)) {
+        StepGraph* g = find_or_capture(ctx, h, u, v, dt, diag_out);
+        if (!g && ctx->pdl) {                             // a driver that cannot capture programmatic edges: plain edges
+            ctx->pdl = false;
+            g = find_or_capture(ctx, h, u, v, dt, diag_out);
+        }
+        if (g) {
             CS_CUDA(ctx, cudaGraphLaunch(g->exec, s));
             ctx->launches += g->launches;
             return CS_OK;

@@ -2,6 +2,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "cs_internal.cuh"
@@ -169,6 +170,7 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
         return bail(cs_fail(ctx, CS_E_NOMEM, "cudaMalloc of reduction scratch failed"));
     cudaMemsetAsync(ctx->d_ticket, 0, sizeof(unsigned int), 0);
     if (cudaDeviceSynchronize() != cudaSuccess) return bail(cs_fail(ctx, CS_E_CUDA, "context set-up failed: %s", cudaGetErrorString(cudaGetLastError())));
+    if (const char* e = std::getenv("CS_PDL")) ctx->pdl = *e != '0';
     *out = ctx;
     return CS_OK;
 }

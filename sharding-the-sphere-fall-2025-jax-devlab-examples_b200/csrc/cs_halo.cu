@@ -29,6 +29,10 @@ __global__ void __launch_bounds__(256)
 halo_fill_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const int32_t* __restrict__ dst,
                  const int32_t* __restrict__ src, const uint8_t* __restrict__ code, const R* __restrict__ rot,
                  int64_t count, int mask) {
+    // launched as a programmatic dependent (cs_launch_dependent): wait for the producer of h, u, v, then let the
+    // consumer's blocks be scheduled while this grid runs
+    cudaGridDependencySynchronize();
+    cudaTriggerProgrammaticLaunchCompletion();
     for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < count; k += (int64_t)gridDim.x * blockDim.x) {
         const int32_t d = dst[k], s = src[k];
         if (mask & 1) h[d] = h[s];
@@ -97,16 +101,16 @@ int grid_for(const cs_ctx* ctx, int64_t count) {
 
 int cs_launch_halo(cs_ctx* ctx, void* h, void* u, void* v, int mask, cudaStream_t s) {
     if (ctx->n_local == 0) return CS_OK;
+    const dim3 grid(grid_for(ctx, ctx->n_local)), block(256);
     if (ctx->dtype == CS_F64)
-        halo_fill_kernel<double><<<grid_for(ctx, ctx->n_local), 256, 0, s>>>((double*)h, (double*)u, (double*)v, ctx->d_halo_dst,
-                                                                            ctx->d_halo_src, ctx->d_halo_code,
-                                                                            (const double*)ctx->d_rot, ctx->n_local, mask);
+        CS_CUDA(ctx, cs_launch_dependent(halo_fill_kernel<double>, grid, block, 0, s, ctx->pdl, (double*)h, (double*)u, (double*)v,
+                                         ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, (const double*)ctx->d_rot,
+                                         (int64_t)ctx->n_local, mask));
     else
-        halo_fill_kernel<float><<<grid_for(ctx, ctx->n_local), 256, 0, s>>>((float*)h, (float*)u, (float*)v, ctx->d_halo_dst,
-                                                                           ctx->d_halo_src, ctx->d_halo_code,
-                                                                           (const float*)ctx->d_rot, ctx->n_local, mask);
+        CS_CUDA(ctx, cs_launch_dependent(halo_fill_kernel<float>, grid, block, 0, s, ctx->pdl, (float*)h, (float*)u, (float*)v,
+                                         ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, (const float*)ctx->d_rot,
+                                         (int64_t)ctx->n_local, mask));
     ctx->launches++;
-    CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;
 }
 

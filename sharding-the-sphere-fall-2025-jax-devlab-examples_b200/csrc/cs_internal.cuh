@@ -64,6 +64,7 @@ struct cs_ctx {
     int4* d_push = nullptr;                      // [T][4] (dst local tile or -1, dst edge, reverse, code)
     bool push_complete = false;                  // every neighbour tile is local
     bool stage_pushed = false;                   // the last stage launch stored the edge ghosts itself
+    bool pdl = false;                            // programmatic dependent launch for stage / halo kernels (CS_PDL=1: on)
 
     // sharded exchange
     std::vector<PeerPlan> peers;
@@ -131,3 +132,18 @@ int cs_launch_pack(cs_ctx* ctx, const void* h, const void* u, const void* v, int
                    cudaStream_t s);
 int cs_launch_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u, void* v, int nfields,
                      cudaStream_t s);
+
+// Launch with the programmatic-stream-serialisation attribute: the kernel may be scheduled while its predecessor
+// in the stream drains and must call cudaGridDependencySynchronize() before it touches anything the predecessor
+// wrote (stage_march_kernel and halo_fill_kernel do; nothing else is launched this way).
+template <typename... KArgs, typename... Args>
+inline cudaError_t cs_launch_dependent(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl,
+                                       Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr, cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}

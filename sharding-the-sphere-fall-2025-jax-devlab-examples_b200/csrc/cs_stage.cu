@@ -166,18 +166,19 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStrea
     // instructions in both precisions, but only fp64 gains (169 -> 154 us at C1536); the fp32 build of it is
     // 7 % SLOWER than the general kernel (87 vs 81 us: a different schedule, not fewer stalls), so fp32 does not use it.
     static const bool unit_variant = env_int("CS_MARCH_UNIT", 1) != 0;
+    const dim3 grid((G.nitems + warps - 1) / warps), block(CS_MARCH_THREADS);
     if (P.push) {
-        stage_march_kernel<R, V, LIM, MINB, true><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, 0, s>>>(P, G);
+        CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, true>, grid, block, 0, s, ctx->pdl, P, G));
     } else {
         bool launched = false;
         if constexpr (sizeof(R) == 8) {
             if (unit_variant && P.a == R(0) && P.b == R(1)) {
-                stage_march_kernel<R, V, LIM, MINB, false, true><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, 0, s>>>(P, G);
+                CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, true>, grid, block, 0, s, ctx->pdl, P, G));
                 launched = true;
             }
         }
         if (!launched)
-            stage_march_kernel<R, V, LIM, MINB, false><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, 0, s>>>(P, G);
+            CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false>, grid, block, 0, s, ctx->pdl, P, G));
     }
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());

@@ -305,6 +305,12 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     const unsigned tbase = (unsigned)t * m * m + col0;   // shards are < 2^31 elements (checked at create)
     using IO = VecIO<R, V>;
 
+    // Launched as a programmatic dependent: everything above (indices, metric constants from tables no kernel writes)
+    // may run while the previous kernel in the stream drains; the state is touched only after this point.  The
+    // trigger lets the next kernel's blocks be scheduled as this grid's blocks retire.
+    cudaGridDependencySynchronize();
+    cudaTriggerProgrammaticLaunchCompletion();
+
     // ---- prologue: rows J0-2 .. J0+1 --------------------------------------------------------
     const int J0 = j0 + g, J1 = j1 + g;
     R hc[V], hp[V], nh[V], uc[V], vc[V], nu[V], nv[V], nt[V];
