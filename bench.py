@@ -188,7 +188,7 @@ def run_reference(args):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ----------------------------------------------------------------------------
@@ -423,7 +423,7 @@ def run_ours(args):
         }
         if secondary:
             line["fp64"] = secondary
-        print(json.dumps(line), flush=True)
+        _emit(line)
     sys.stdout.flush()
     if world > 1:
         # a rank that is slow to tear NCCL down must not hold the job: hard exit after a grace period
@@ -434,8 +434,26 @@ def run_ours(args):
         os._exit(0)
 
 
+_RESULT_FD = None
+
+
+def _emit(line):
+    """The one JSON line goes to the process's original stdout; everything else that writes to fd 1 during the run
+    (NCCL prints its version banner there) has been sent to stderr."""
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    global _RESULT_FD
     args = parse_args()
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
