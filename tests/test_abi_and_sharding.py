@@ -33,6 +33,21 @@ def test_config_struct_matches_header():
     assert fields == [f[0] for f in _binding.CsConfig._fields_]
 
 
+def test_header_is_plain_c(tmp_path):
+    """The boundary is a C ABI: the header must compile as C99 with nothing but the C library."""
+    import shutil
+    import subprocess
+    gcc = "/usr/bin/gcc" if Path("/usr/bin/gcc").exists() else shutil.which("gcc")
+    if not gcc:
+        pytest.skip("no C compiler")
+    src = tmp_path / "t.c"
+    src.write_text('#include "cubesphere.h"\nint main(void) { struct cs_config c; c.N = 1; return cs_abi_version() == c.N; }\n')
+    inc = Path(__file__).resolve().parents[1] / "include"
+    r = subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", f"-I{inc}", str(src)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
 def test_no_cpu_fallback(built_library):
     """Without a CUDA device context creation fails with CS_E_CUDA and a clear message."""
     import torch
