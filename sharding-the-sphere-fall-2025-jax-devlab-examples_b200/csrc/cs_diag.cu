@@ -9,6 +9,7 @@
 namespace {
 
 constexpr int DIAG_THREADS = 256;
+constexpr int DIAG_UNROLL = 4;
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -52,15 +53,33 @@ diag_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restric
         for (int j = j0; j < j1; ++j) {
             const double Y = xt_y[j];
             const size_t row = (size_t)t * m * m + (size_t)(j + g) * m + g;
-            for (int i = threadIdx.x; i < n; i += DIAG_THREADS) {
-                const size_t o = row + i;
-                const Metric<double> M = cs_metric<double>(xt_x[i], Y, a2);
-                const double hh = (double)h[o], uu = (double)u[o], vv = (double)v[o];
-                const double hs = topo ? (double)topo[o] : 0.0;
-                const Derived<double> D = cs_derive<double>(M, hh, uu, vv, hs, grav);
-                const double w = M.sg * darea;
-                mass += w * hh;
-                energy += w * (hh * D.K + 0.5 * grav * hh * hh + grav * hh * hs);
+            // DIAG_UNROLL cells per thread and pass, all loads issued before the arithmetic: the kernel is bound by
+            // memory latency (32 resident warps per SM, a chain of ~40 dependent fp64 operations per cell), so bytes
+            // in flight per thread are what count.  Cells past the end of the row are loaded from a valid address
+            // and zeroed: adding 0.0 leaves the sums bit-identical, and every thread's order stays fixed.
+            for (int i0 = threadIdx.x; i0 < n; i0 += DIAG_UNROLL * DIAG_THREADS) {
+                R hq[DIAG_UNROLL], uq[DIAG_UNROLL], vq[DIAG_UNROLL], tq[DIAG_UNROLL];
+                double Xq[DIAG_UNROLL];
+#pragma unroll
+                for (int k = 0; k < DIAG_UNROLL; ++k) {
+                    const int i = i0 + k * DIAG_THREADS;
+                    const int ic = i < n ? i : i0;
+                    const size_t o = row + ic;
+                    hq[k] = h[o], uq[k] = u[o], vq[k] = v[o];
+                    tq[k] = topo ? topo[o] : R(0);
+                    Xq[k] = xt_x[ic];
+                }
+#pragma unroll
+                for (int k = 0; k < DIAG_UNROLL; ++k) {
+                    const bool in = i0 + k * DIAG_THREADS < n;
+                    const Metric<double> M = cs_metric<double>(Xq[k], Y, a2);
+                    const double hh = in ? (double)hq[k] : 0.0, uu = (double)uq[k], vv = (double)vq[k];
+                    const double hs = (double)tq[k];
+                    const Derived<double> D = cs_derive<double>(M, hh, uu, vv, hs, grav);
+                    const double w = M.sg * darea;
+                    mass += w * hh;
+                    energy += w * (hh * D.K + 0.5 * grav * hh * hh + grav * hh * hs);
+                }
             }
         }
     }
