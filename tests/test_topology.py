@@ -190,3 +190,65 @@ def test_state_files_round_trip(tmp_path):
     assert (meta["N"], meta["tiles_per_edge"], meta["halo"], meta["step"], meta["time"], meta["case"]) == (12, 2, 2, 7, 123.5, "tc2")
     with pytest.raises(ValueError):
         io.save_state(tmp_path / "bad.npz", state, N=16, halo=2)
+
+
+# ---- property tests (hypothesis) -------------------------------------------------------------------
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+
+@settings(max_examples=200, deadline=None)
+@given(face=st.integers(0, 5), N=st.integers(4, 40), g=st.integers(1, 3), data=st.data())
+def test_resolve_lands_inside_the_neighbour_and_mirrors_back(face, N, g, data):
+    """A ghost cell across one edge resolves to an interior cell of the neighbour within depth g of the shared edge;
+    the neighbour's ghost at the mirrored position resolves back to our boundary cell with the inverse code."""
+    e = data.draw(st.sampled_from(topology.EDGES))
+    d = data.draw(st.integers(0, g - 1))
+    k = data.draw(st.integers(0, N - 1))
+    J, I = {"N": (N + d, k), "S": (-1 - d, k), "E": (k, N + d), "W": (k, -1 - d)}[e]
+    fb, Jb, Ib, code = (int(x) for x in topology.resolve(face, J, I, N))
+    f2, e2, rev, S = topology.neighbour(face, e)
+    assert fb == f2 and 0 <= Jb < N and 0 <= Ib < N and code == topology.perm_code(S)
+    depth = {"N": N - 1 - Jb, "S": Jb, "E": N - 1 - Ib, "W": Ib}[e2]
+    assert depth == d                                              # ghost depth d <- interior depth d
+    # our interior cell at depth d next to the edge, seen from the neighbour's ghost zone
+    along = Ib if e2 in ("N", "S") else Jb
+    Jg, Ig = {"N": (N + d, along), "S": (-1 - d, along), "E": (along, N + d), "W": (along, -1 - d)}[e2]
+    f0, J0, I0, code_back = (int(x) for x in topology.resolve(f2, Jg, Ig, N))
+    assert f0 == face
+    ours = {"N": (N - 1 - d, k), "S": (d, k), "E": (k, N - 1 - d), "W": (k, d)}[e]
+    assert (J0, I0) == ours
+    u, v = np.array([3.0]), np.array([-5.0])
+    a, b = partition.apply_code(*partition.apply_code(u, v, np.array([code])), np.array([code_back]))
+    assert a[0] == u[0] and b[0] == v[0]                            # there and back: the identity on vectors
+
+
+@settings(max_examples=60, deadline=None)
+@given(p=st.integers(1, 4), world=st.integers(1, 24))
+def test_block_ranges_partition_or_reject(p, world):
+    T = topology.num_tiles(p)
+    if world > T or T % world:
+        with pytest.raises(ValueError):
+            partition.block_ranges(T, world)
+        return
+    ranges = partition.block_ranges(T, world)
+    assert len(ranges) == world and ranges[0][0] == 0 and sum(c for _, c in ranges) == T
+    assert all(b2 == b1 + c1 for (b1, c1), (b2, _) in zip(ranges, ranges[1:]))
+    assert len({c for _, c in ranges}) == 1
+
+
+@settings(max_examples=25, deadline=None)
+@given(p=st.integers(1, 3), n=st.integers(2, 5), g=st.integers(1, 2))
+def test_halo_table_covers_every_ghost_cell_once(p, n, g):
+    N = n * p
+    if g > n:
+        return
+    tab = topology.build_halo_table(N, p, g)
+    m = n + 2 * g
+    T = topology.num_tiles(p)
+    ghosts = T * (m * m - n * n)
+    assert len(tab["dst_tile"]) == ghosts
+    key = tab["dst_tile"] * m * m + tab["dst_j"] * m + tab["dst_i"]
+    assert len(np.unique(key)) == ghosts                            # one writer per ghost cell
+    sj, si = tab["src_j"], tab["src_i"]
+    assert np.all((sj >= g) & (sj < g + n) & (si >= g) & (si < g + n))   # sources are interior cells only
+    assert set(np.unique(tab["code"])) <= set(range(8))
