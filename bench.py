@@ -149,6 +149,8 @@ def cpu_run(case, dt, steps, warmup):
     from oracle import cs_oracle_c as occ
     from oracle import cs_oracle_np as orc
     N, g = case.N, 2
+    # every core this process may run on, whatever OMP_NUM_THREADS says (torchrun sets it to 1 for its workers)
+    occ.set_threads(len(os.sched_getaffinity(0)))
     hs = None
     if case.hs is not None:
         hs = orc.halo_fill_scalar(orc.pad(case.hs, g), g)

@@ -278,6 +278,15 @@ void cso_diagnostics(cso_ctx* c, const double* h, const double* u, const double*
     out[0] = mass, out[1] = energy;
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the timed baseline asks for the cores it may use */
+void cso_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int cso_num_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

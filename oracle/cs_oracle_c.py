@@ -36,8 +36,14 @@ def lib():
         h.cso_diagnostics.argtypes = [C.c_void_p, dp, dp, dp, dp]
         h.cso_halo_fill.argtypes = [C.c_int, C.c_int, dp, dp, dp]
         h.cso_num_threads.restype = C.c_int
+        h.cso_set_num_threads.argtypes = [C.c_int]
         _lib = h
     return _lib
+
+
+def set_threads(n):
+    """Number of OpenMP threads for the following calls (the timed baseline uses every core it is allowed)."""
+    lib().cso_set_num_threads(int(n))
 
 
 def _p(a):
