@@ -1,6 +1,7 @@
 """Command-line driver: integrate one of the test cases on one GPU and print the conservation diagnostics.
 
     python -m cubesphere.run --case tc5 --N 384 --hours 24 --dtype f64 [--restart out.npz]
+    python -m cubesphere.run --resume out.npz --hours 24 [--restart out2.npz]      # carry on from a restart file
 
 A thin example of the public API (cases -> Context -> step -> diagnostics -> restart file); the hot path is
 entirely inside the C ABI calls.
@@ -23,12 +24,21 @@ def main(argv=None):
     ap.add_argument("--limiter", default="mc", choices=["none", "minmod", "mc"])
     ap.add_argument("--report-every", type=int, default=50)
     ap.add_argument("--restart", default=None, help="write the final state to this .npz file")
+    ap.add_argument("--resume", default=None, help="start from this restart file (case, N, dtype are taken from it)")
     args = ap.parse_args(argv)
 
     import torch
     from . import api, cases, io
 
     g = 2
+    resumed, step0, time0 = None, 0, 0.0
+    if args.resume:
+        resumed, meta = io.load_state(args.resume)
+        if meta["tiles_per_edge"] != 1 or meta["halo"] != g or not meta.get("case"):
+            raise ValueError(f"{args.resume}: need a whole-face state with halo {g} and a named case")
+        args.case, args.N = meta["case"], meta["N"]
+        args.dtype = "f32" if meta["dtype"] == "float32" else "f64"
+        step0, time0 = meta["step"], meta["time"]
     case = cases.make_case(args.case, args.N)
     dt = cases.stable_dt(case, args.cfl)
     nsteps = max(1, int(round(args.hours * 3600.0 / dt)))
@@ -40,25 +50,30 @@ def main(argv=None):
         out[:, g:-g, g:-g] = x
         return torch.from_numpy(out).cuda()
 
-    h, u, v = padded(case.h), padded(case.u1), padded(case.u2)
+    if resumed is None:
+        h, u, v = padded(case.h), padded(case.u1), padded(case.u2)
+    else:
+        h, u, v = (torch.from_numpy(np.ascontiguousarray(resumed[k], dtype=ndt)).cuda() for k in ("h", "u", "v"))
     if case.hs is not None:
         ctx.set_topography(padded(case.hs))
     ctx.halo_fill_state(h, u, v)
     d0 = ctx.diagnostics(h, u, v).cpu().numpy()
-    print(f"{args.case} C{args.N} {args.dtype}: dt = {dt:.2f} s, {nsteps} steps, mass0 = {d0[0]:.6e}, energy0 = {d0[1]:.6e}")
+    print(f"{args.case} C{args.N} {args.dtype}: dt = {dt:.2f} s, {nsteps} steps from step {step0}, "
+          f"mass0 = {d0[0]:.6e}, energy0 = {d0[1]:.6e}")
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for k in range(1, nsteps + 1):
         ctx.step(h, u, v, dt)
         if k % args.report_every == 0 or k == nsteps:
             d = ctx.diagnostics(h, u, v).cpu().numpy()
-            print(f"  step {k:6d}  t = {k * dt / 3600.0:8.2f} h  mass drift = {(d[0] - d0[0]) / d0[0]:+.2e}  "
+            print(f"  step {step0 + k:6d}  t = {(time0 + k * dt) / 3600.0:8.2f} h  mass drift = {(d[0] - d0[0]) / d0[0]:+.2e}  "
                   f"energy drift = {(d[1] - d0[1]) / d0[1]:+.2e}  h in [{float(h.min()):.2f}, {float(h.max()):.2f}]")
     torch.cuda.synchronize()
     sec = time.perf_counter() - t0
     print(f"{6.0 * args.N ** 2 * nsteps / sec / 1e9:.2f} G cell-updates/s including the diagnostics read-backs")
     if args.restart:
-        io.save_state(args.restart, {"h": h, "u": u, "v": v}, N=args.N, halo=g, step=nsteps, time=nsteps * dt, case=args.case)
+        io.save_state(args.restart, {"h": h, "u": u, "v": v}, N=args.N, halo=g, step=step0 + nsteps,
+                      time=time0 + nsteps * dt, case=args.case)
         print(f"state written to {args.restart}")
     ctx.close()
 

@@ -502,3 +502,19 @@ def test_step_host_batch_equals_single_calls(built_library, copy_back):
     with pytest.raises(ValueError):
         ctx.step_host_batch([members[0][:2] + [members[0][0][:, :-1]]], dt)
     ctx.close()
+
+
+def test_cli_resume_continues_bit_for_bit(built_library, tmp_path, capsys):
+    """python -m cubesphere.run: 1 h (6 steps) + restart file + 1 h resumed == 2 h (12 steps) in one go: same bits,
+    same step counter."""
+    from cubesphere import io, run
+    a, b, c = (str(tmp_path / f"{n}.npz") for n in "abc")
+    run.main(["--case", "tc5", "--N", "24", "--hours", "1", "--restart", a])
+    run.main(["--resume", a, "--hours", "1", "--restart", b])
+    run.main(["--case", "tc5", "--N", "24", "--hours", "2", "--restart", c])
+    sb, mb = io.load_state(b)
+    sc, mc = io.load_state(c)
+    assert mb["step"] == mc["step"] == 12 and abs(mb["time"] - mc["time"]) <= 1e-9 * mc["time"] and mb["case"] == "tc5"
+    for k in ("h", "u", "v"):
+        assert np.array_equal(sb[k], sc[k])
+    assert "from step" in capsys.readouterr().out
