@@ -185,3 +185,37 @@ def test_bench_reference_arm_prints_one_contract_line():
     assert d["impl"] == "reference" and d["value"] > 0 and d["unit"] == "cell-updates/s" and d["steps"] == 1
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+
+
+def _build_abi_demo(tmp_path):
+    import shutil
+    gcc = "/usr/bin/gcc" if Path("/usr/bin/gcc").exists() else shutil.which("gcc")
+    if not gcc:
+        pytest.skip("no C compiler")
+    libdir = ROOT / "sharding-the-sphere-fall-2025-jax-devlab-examples_b200" / "lib"
+    exe = tmp_path / "abi_demo"
+    r = subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", f"-I{ROOT / 'include'}", str(ROOT / "examples" / "abi_demo.c"),
+                        f"-L{libdir}", "-lcubesphere_b200", f"-Wl,-rpath,{libdir}", "-lm", "-o", str(exe)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_c_caller_links_and_fails_loudly_without_a_gpu(built_library, tmp_path):
+    """examples/abi_demo.c is a complete plain-C caller of the header: it must compile and link against the shared
+    library with a C compiler alone, and without a CUDA device report the library's 'no CPU fallback' error."""
+    import torch
+    exe = _build_abi_demo(tmp_path)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present: covered by the gpu-marked test")
+    r = subprocess.run([str(exe), "24", "2"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 2 and "no CPU fallback" in r.stderr, (r.returncode, r.stderr)
+
+
+@pytest.mark.gpu
+def test_c_caller_runs_on_the_gpu(built_library, tmp_path):
+    """The same program on a GPU: a resting layer stays exactly at rest and its mass is 4 pi a^2 h to O(1/N^2)."""
+    exe = _build_abi_demo(tmp_path)
+    r = subprocess.run([str(exe), "48", "10"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    assert "max |h - h0| = 0.000e+00" in r.stdout and "max |u| = 0.000e+00" in r.stdout, r.stdout
