@@ -51,6 +51,9 @@ def parse_args():
     ap.add_argument("--kernel", default="auto")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the fp64 side measurement")
+    ap.add_argument("--new-state-sums", action="store_true",
+                    help="per-step mass / energy of the NEW state (summed in the last stage) instead of the entry state (first stage)")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the multi-GPU parity run that precedes the timing")
     return ap.parse_args()
 
 
@@ -144,18 +147,21 @@ def faces_to_padded_tiles(field, p, g, dtype):
 # CPU arm (oracle; bench.py's cpu_baseline leg and the --impl reference arm)
 # ----------------------------------------------------------------------------
 
-def cpu_run(case, dt, steps, warmup):
-    """Time `steps` steps of the C/OpenMP oracle after `warmup` steps.  Returns (cell-updates/s, threads, seconds)."""
+def cpu_run(case, dt, steps, warmup, dtype="f64"):
+    """Time `steps` steps of the C/OpenMP oracle after `warmup` steps, in the named precision (the fp32 build is the
+    same source with the state, the tables and the per-cell arithmetic in float).
+    Returns (cell-updates/s, threads, seconds)."""
     from oracle import cs_oracle_c as occ
     from oracle import cs_oracle_np as orc
     N, g = case.N, 2
+    nd = np.float32 if dtype == "f32" else np.float64
     # every core this process may run on, whatever OMP_NUM_THREADS says (torchrun sets it to 1 for its workers)
-    occ.set_threads(len(os.sched_getaffinity(0)))
+    occ.set_threads(len(os.sched_getaffinity(0)), nd)
     hs = None
     if case.hs is not None:
-        hs = orc.halo_fill_scalar(orc.pad(case.hs, g), g)
-    co = occ.COracle(N, g, axis=case.axis, advect_only=case.advect_only, hs=hs)
-    st = [np.ascontiguousarray(orc.pad(x, g)) for x in (case.h, case.u1, case.u2)]
+        hs = orc.halo_fill_scalar(orc.pad(case.hs, g), g).astype(nd)
+    co = occ.COracle(N, g, axis=case.axis, advect_only=case.advect_only, hs=hs, dtype=nd)
+    st = [np.ascontiguousarray(orc.pad(x, g).astype(nd)) for x in (case.h, case.u1, case.u2)]
     occ.halo_fill(N, g, st[0], st[1], st[2])
     if warmup:
         co.step(*st, dt, warmup)
@@ -176,16 +182,16 @@ def run_reference(args):
     N_job = args.N or WEAK_N.get(args.gpus, 1536)
     N = min(N_job, 1536)
     case, dt = initial_state(args.case, N)
-    val, threads, sec = cpu_run(case, dt, args.steps, args.warmup)
-    sample = f"{args.steps} full fp64 steps of {args.case} C{N} after {args.warmup} warm-up"
+    val, threads, sec = cpu_run(case, dt, args.steps, args.warmup, args.dtype)
+    sample = f"{args.steps} full {args.dtype} steps of {args.case} C{N} after {args.warmup} warm-up, C + OpenMP oracle"
     if N != N_job:
         sample += f" (bounded sample of the C{N_job} job)"
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"{args.case} C{N_job}, SSP-RK3 (3 fused stages + halo) per step, {args.dtype}",
-                   "N": N_job, "halo": 2, "run_as": f"C{N} fp64 on the host cores"},
+                   "N": N_job, "halo": 2, "run_as": f"C{N} {args.dtype} on the host cores"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -196,6 +202,93 @@ def run_reference(args):
 # ----------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------
+
+def multi_gpu_parity(rank, world, local):
+    """BASELINE configs[2] on the GPUs the job runs on: Williamson case 5 (flow over the mountain), C384, fp64,
+    2 x 2 tiles per face block-partitioned over the ranks, 20 steps through the sharded stepper exactly as the
+    timed loop drives it (rim / inner split, NCCL exchange overlapped, the step replayed as a CUDA graph), gathered
+    to rank 0 and compared there with the C oracle on the host.  Also one sharded ghost fill of random numbers
+    against the oracle's fill, bit for bit.  Returns the record on rank 0 (None elsewhere); the caller fails the
+    run when a tolerance of BASELINE.json (rel-L2(h) <= 1e-12, mass 1e-13, halo bit-exact) is missed."""
+    import torch
+    import torch.distributed as dist
+    from cubesphere import cases, sharded
+    N, p, g, steps = 384, 2, 2, 20
+    case = cases.make_case("tc5", N)
+    dt = cases.stable_dt(case, 0.5)
+    tang = None
+    if rank == 0:
+        from oracle import cs_oracle_np as orc            # the checker (rank 0 only)
+        tang = orc.centre_tangents(N)
+    box = [tang]
+    dist.broadcast_object_list(box, src=0)                # every rank builds its tables from the oracle's tangents
+    st = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis, device=local, rank=rank,
+                                world=world, tangents=box[0])
+    b, c = st.tile_begin, st.tile_count
+    n = N // p
+
+    def shard(face_field):                                # [6, N, N] interior -> this rank's padded tiles, ghosts zero
+        out = np.zeros((c, n + 2 * g, n + 2 * g))
+        for k in range(c):
+            t = b + k
+            f, ty, tx = t // (p * p), (t % (p * p)) // p, t % p
+            out[k, g:g + n, g:g + n] = face_field[f, ty * n:(ty + 1) * n, tx * n:(tx + 1) * n]
+        return out
+
+    def gather(tensors):                                  # list of [c, m, m] device tensors -> [24, m, m] arrays on rank 0
+        res = []
+        for x in tensors:
+            parts = [torch.empty_like(x) for _ in range(world)] if rank == 0 else None
+            dist.gather(x, parts, dst=0)
+            res.append(torch.cat(parts).cpu().numpy() if rank == 0 else None)
+        return res
+
+    # (1) ghost fill of random numbers, bit for bit
+    rng = np.random.default_rng(20251118)
+    rnd = [rng.standard_normal((6, N, N)) for _ in range(3)]
+    dev = [torch.from_numpy(shard(x)).cuda() for x in rnd]
+    st.halo_fill(*dev)
+    got = gather(dev)
+    halo_ok = None
+    if rank == 0:
+        want = orc.halo_fill_state(*(orc.pad(x, g) for x in rnd), g)
+        halo_ok = all(np.array_equal(a, orc.faces_to_tiles(w, p, g)) for a, w in zip(got, want))
+    # (2) 20 steps of case 5
+    dev = [torch.from_numpy(shard(x)).cuda() for x in (case.h, case.u1, case.u2)]
+    st.set_topography(torch.from_numpy(shard(case.hs)).cuda())
+    st.halo_fill(*dev)
+    m0 = st.diagnostics(*dev).cpu().numpy()
+    for _ in range(steps):
+        st.step(*dev, dt)
+    m1 = st.diagnostics(*dev).cpu().numpy()
+    got = gather(dev)
+    rec = None
+    if rank == 0:
+        from oracle import cs_oracle_c as occ
+        occ.set_threads(len(os.sched_getaffinity(0)))
+        hs = orc.halo_fill_scalar(orc.pad(case.hs, g), g)
+        co = occ.COracle(N, g, axis=case.axis, hs=hs)
+        ref = [np.ascontiguousarray(orc.pad(x, g)) for x in (case.h, case.u1, case.u2)]
+        occ.halo_fill(N, g, *ref)
+        mo0 = co.diagnostics(*ref)
+        co.step(*ref, dt, steps)
+        mo1 = co.diagnostics(*ref)
+        cc = slice(g, g + N)
+        errs = []
+        for a, w in zip(got, ref):
+            a = orc.tiles_to_faces(a, p, g)
+            errs.append(float(np.linalg.norm(a[:, cc, cc] - w[:, cc, cc]) / np.linalg.norm(w[:, cc, cc])))
+        rec = {"config": f"tc5 C{N} fp64, {6 * p * p} tiles over {world} GPUs, {steps} steps, graph replay + overlap, vs oracle/cs_oracle.c",
+               "rel_l2_h": errs[0], "rel_l2_u": errs[1], "rel_l2_v": errs[2],
+               "mass_drift": float((m1[0] - m0[0]) / m0[0]), "mass_vs_oracle": float(abs(m1[0] - mo1[0]) / mo1[0]),
+               "energy_vs_oracle": float(abs(m1[1] - mo1[1]) / mo1[1]), "oracle_mass_drift": float((mo1[0] - mo0[0]) / mo0[0]),
+               "halo_bit_exact": bool(halo_ok)}
+        rec["ok"] = bool(halo_ok and errs[0] <= 1e-12 and abs(rec["mass_drift"]) <= 1e-13 and rec["mass_vs_oracle"] <= 1e-13)
+    st.close()
+    del dev
+    torch.cuda.empty_cache()
+    return rec
+
 
 def run_ours(args):
     import torch
@@ -213,10 +306,22 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
+    # ---- multi-GPU parity on the hardware the numbers come from (before anything is timed) ------------------
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = multi_gpu_parity(rank, world, local)
+        flag = torch.tensor([1 if (rank != 0 or parity["ok"]) else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) != 1:
+            if rank == 0:
+                sys.stderr.write("multi-GPU parity FAILED: " + json.dumps(parity) + "\n")
+                _emit({"metric": METRIC, "value": None, "n_gpus": world, "parity": parity, "error": "multi-GPU parity failed"})
+            dist.destroy_process_group()
+            os._exit(3)
+
     N = args.N or WEAK_N.get(world, 1536)
     p = WEAK_P.get(world, 1) if not args.N else (2 if world > 2 else 1)
     g = 2
-    tdtype = torch.float32 if args.dtype == "f32" else torch.float64
     ndtype = np.float32 if args.dtype == "f32" else np.float64
     esize = 4 if args.dtype == "f32" else 8
     ranges = partition.block_ranges(6 * p * p, world)
@@ -229,9 +334,10 @@ def run_ours(args):
         tdt = torch.tensor([dt], device="cuda", dtype=torch.float64)
         dist.all_reduce(tdt, op=dist.ReduceOp.MIN)
         dt = float(tdt.item())
+    # conservation sums every step, taken inside the first stage's launches (the state each step starts from)
     stepper = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
                                      advect_only=case.advect_only, device=local, rank=rank, world=world,
-                                     kernel=args.kernel)
+                                     kernel=args.kernel, sums_of_entry_state=not args.new_state_sums)
     assert (stepper.tile_begin, stepper.tile_count) == (t0, tc)
 
     def padded(field):
@@ -247,59 +353,81 @@ def run_ours(args):
     stepper.halo_fill(*dev)
     cells_total = 6.0 * N * N
     cells_local = float(tc) * stepper.n * stepper.n
+    diag = torch.zeros(2, dtype=torch.float64, device="cuda")
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident throughput ------------------------------------------------------
+    def one_step(with_sums=True):
+        # N = 1: cs_step(..., diag_out) -- halo fills, three fused stages, conservation sums out of the last one
+        if world == 1:
+            stepper.ctx.step(*dev, dt, diag=diag if with_sums else None)
+        else:
+            stepper.step(*dev, dt, diag=diag if with_sums else None)
+
+    def timed_steps(k, with_sums=True):
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        l0 = stepper.launches
+        ev0.record()
+        for _ in range(k):
+            one_step(with_sums)
+        ev1.record()
+        barrier()
+        t_ms = ev0.elapsed_time(ev1)
+        if world > 1:
+            t = torch.tensor([t_ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            t_ms = float(t.item())
+        return t_ms, stepper.launches - l0
+
+    # ---- device-resident throughput: the whole step, conservation sums included ----------------------------
     for _ in range(args.warmup):
-        stepper.step(*dev, dt)
+        one_step()
     barrier()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     clk = ClockSampler(local).start()
     time.sleep(0.15)                               # let the sampler come up; the GPU is warm from the warm-up steps
     for _ in range(args.warmup):
-        stepper.step(*dev, dt)
-    barrier()
-    l0 = stepper.launches
-    ev0.record()
-    for _ in range(args.steps):
-        stepper.step(*dev, dt)
-    ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    launches = stepper.launches - l0
-    if world > 1:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        one_step()
+    ms, launches = timed_steps(args.steps)
     value = cells_total * args.steps / (ms * 1e-3)
-    finite = bool(torch.isfinite(dev[0]).all().item())
+    d_after = diag.cpu().numpy().tolist()
+    finite = bool(torch.isfinite(dev[0]).all().item()) and bool(np.isfinite(d_after).all())
+    for _ in range(2):
+        one_step(False)
+    ms_nosums, _ = timed_steps(args.steps, with_sums=False)
 
-    # ---- roofline of the dominant kernel (fused RK stage), timed per launch ------------------
+    # ---- roofline of the dominant kernel (fused RK stage), timed per launch inside a CUDA graph --------------
     peak, peak_kind = measured_peak_gbs()
-    roof = stepper.time_stage_kernel(dev, dt, reps=max(3, min(args.steps, 10)))
+    roof = stepper.time_stage_kernel(dev, dt, reps=10)
     words = {True: 6, False: 9}                    # stage 1 reads qs, writes out; later stages also read q0
     alg_bytes = sum(words[a == 0.0] for a in roof["a"]) * esize * cells_local
     achieved = alg_bytes / (sum(roof["ms"]) * 1e-3) / 1e9
     # traffic: dram__bytes_read + dram__bytes_write per launch from the committed `ncu --set full` capture of
-    # this kernel (profiles/r01_traffic.json); only quoted when the capture's configuration is the one running
+    # this kernel (profiles/r0N_traffic.json); only quoted when the capture's configuration is the one running
     traffic = None
-    try:
-        tr = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())
-        key = f"{args.dtype}_C{N}_tiles{tc}"
-        if key in tr:
-            traffic = tr[key]["dram_bytes_per_launch"]
-    except Exception:
-        pass
+    for name in ("r02_traffic.json", "r01_traffic.json"):
+        try:
+            tr = json.loads((ROOT / "profiles" / name).read_text())
+            key = f"{args.dtype}_C{N}_tiles{tc}"
+            if key in tr:
+                traffic = tr[key]["dram_bytes_per_launch"]
+                break
+        except Exception:
+            pass
+    step_bytes = 24 * esize * cells_total / world
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_kind": peak_kind, "kernel": roof["kernel"],
+                "traffic": traffic, "peak_kind": peak_kind, "kernel": roof["kernel"], "timing": roof["how"],
                 "algorithmic_bytes_per_launch": alg_bytes / len(roof["ms"]),
                 "algorithmic_bytes_per_cell_step": 24 * esize,
-                "stage_ms": [float(x) for x in roof["ms"]], "frac_of_nominal_8TBs": achieved / 8000.0,
-                "whole_step_frac": 24 * esize * cells_total / world / (ms / args.steps * 1e-3) / 1e9 / peak}
+                "stage_ms": [float(x) for x in roof["ms"]],
+                "stage_frac": [words[a == 0.0] * esize * cells_local / (t * 1e-3) / 1e9 / peak for a, t in zip(roof["a"], roof["ms"])],
+                "fused_sums_us": roof["fused_sums_us"],
+                "frac_of_nominal_8TBs": achieved / 8000.0,
+                "whole_step_frac": step_bytes / (ms / args.steps * 1e-3) / 1e9 / peak,
+                "whole_step_frac_without_sums": step_bytes / (ms_nosums / args.steps * 1e-3) / 1e9 / peak}
 
     # ---- halo: the ghost-fill launch alone, and what the step pays beyond its three stage kernels -------
     halo = None
@@ -323,51 +451,54 @@ def run_ours(args):
         fill_us = hev0.elapsed_time(hev1) * 1e3 / 200
         del hgraph
         halo = {"fill_us": fill_us, "fills_per_step": len(roof["ms"]), "halo_us_per_step": fill_us * len(roof["ms"]),
-                "exposed_us_per_step": max(0.0, (ms / args.steps - sum(roof["ms"])) * 1e3)}
+                "exposed_us_per_step": max(0.0, (ms_nosums / args.steps - sum(roof["ms"])) * 1e3)}
+    else:
+        h = stepper.time_halo(dev, dt, reps=max(10, args.steps))
+        halo = {"exchange_us": h["exchange_us"], "fills_per_step": len(roof["ms"]),
+                "halo_us_per_step": h["exchange_us"] * len(roof["ms"]),
+                "step_ms_without_exchange": h["step_ms_without_exchange"],
+                "exposed_us_per_step": (ms_nosums / args.steps - h["step_ms_without_exchange"]) * 1e3,
+                "what": "exchange_us = pack + NCCL all-to-all + unpack of one ghost fill, alone on an idle GPU, max over ranks; "
+                        "exposed = step time minus the time of the same step with the cross-GPU exchange left out",
+                "path": stepper.halo_path}
 
-    # ---- end to end through the host-buffer entry point ---------------------------------------
+    # ---- end to end through the host-buffer entry point: a ROUND TRIP (state in, new state + sums out) --------
     e2e = None
     if world == 1:
         ctx = stepper.ctx
         n_e2e = max(3, min(args.steps, 5))
-        ctx.step_host(*pinned, dt, nsteps=1, copy_back=False)            # warm-up (allocates the device copy)
+        nbytes = sum(x.numel() * x.element_size() for x in pinned)
+        ctx.step_host(*pinned, dt, nsteps=1, copy_back=True)             # warm-up (allocates the device copy)
         torch.cuda.synchronize()
+        scratch = [x.clone().pin_memory() for x in pinned]               # the single-call legs advance a copy
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(n_e2e):
-            ctx.step_host(*pinned, dt, nsteps=1, copy_back=False)        # H2D state, step, D2H [mass, energy]
+            ctx.step_host(*scratch, dt, nsteps=1, copy_back=True)        # H2D state, step, D2H state + [mass, energy]
         e1.record()
         torch.cuda.synchronize()
-        ms_a = e0.elapsed_time(e1) / n_e2e
-        e0.record()
-        for _ in range(n_e2e):
-            ctx.step_host(*pinned, dt, nsteps=1, copy_back=True)         # ... and the whole state back
-        e1.record()
-        torch.cuda.synchronize()
-        ms_b = e0.elapsed_time(e1) / n_e2e
-        nbytes = sum(x.numel() * x.element_size() for x in pinned)
+        ms_single = e0.elapsed_time(e1) / n_e2e
         # The headline goes through the batch entry point: 8 members (2 distinct pinned states) stream through two
         # device slots, so the upload of member i + 1 and the download of member i - 1 overlap the step of member i.
-        # Every member's state is copied host -> device and its [mass, energy] (round_trip: its whole state)
-        # device -> host inside the timed region.  The one-state-per-call number is reported beside it.
-        ens = [pinned, [x.clone().pin_memory() for x in pinned]] * 4
-        ctx.step_host_batch(ens, dt, nsteps=1, copy_back=False)          # warm-up (second slot, streams, graphs)
-        t0 = time.perf_counter()
-        ctx.step_host_batch(ens, dt, nsteps=1, copy_back=False)
-        ms_c = (time.perf_counter() - t0) * 1e3 / len(ens)
-        t0 = time.perf_counter()
+        # Every member's state is copied host -> device, stepped, and its NEW STATE and [mass, energy] are copied
+        # device -> host inside the timed region (step(state, dt) returns the state).
+        ens = [scratch, [x.clone().pin_memory() for x in pinned]] * 4
+        ctx.step_host_batch(ens, dt, nsteps=1, copy_back=True)           # warm-up (second slot, streams, graphs)
+        t0_ = time.perf_counter()
         ctx.step_host_batch(ens, dt, nsteps=1, copy_back=True)
-        ms_d = (time.perf_counter() - t0) * 1e3 / len(ens)
-        del ens
-        e2e = {"value": cells_total / (ms_c * 1e-3), "unit": UNIT, "h2d_bytes_per_step": nbytes,
-               "d2h_bytes_per_step": 16, "ms_per_step": ms_c,
-               "call": "cs_step_host_batch: 8 members, 1 step each (H2D state, halo fill, step, D2H [mass, energy]), "
-                       "copies overlapped with the neighbours' steps; host wall clock around the blocking call",
-               "round_trip": {"value": cells_total / (ms_d * 1e-3), "h2d_bytes_per_step": nbytes,
-                              "d2h_bytes_per_step": nbytes + 16, "ms_per_step": ms_d},
-               "single_call": {"call": "cs_step_host: one state per call, nothing overlapped; CUDA events",
-                               "value": cells_total / (ms_a * 1e-3), "ms_per_step": ms_a,
-                               "round_trip": {"value": cells_total / (ms_b * 1e-3), "ms_per_step": ms_b}}}
+        ms_rt = (time.perf_counter() - t0_) * 1e3 / len(ens)
+        t0_ = time.perf_counter()
+        ctx.step_host_batch(ens, dt, nsteps=1, copy_back=False)
+        ms_up = (time.perf_counter() - t0_) * 1e3 / len(ens)
+        del ens, scratch
+        e2e = {"value": cells_total / (ms_rt * 1e-3), "unit": UNIT, "h2d_bytes_per_step": nbytes,
+               "d2h_bytes_per_step": nbytes + 16, "ms_per_step": ms_rt,
+               "call": "cs_step_host_batch(copy_back=1): 8 members, 1 step each -- H2D state, halo fill, step, D2H new state "
+                       "+ [mass, energy]; copies overlapped with the neighbours' steps; host wall clock around the blocking call",
+               "sums_only": {"value": cells_total / (ms_up * 1e-3), "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 16,
+                             "ms_per_step": ms_up, "what": "same call with copy_back=0: only [mass, energy] come back"},
+               "single_call": {"call": "cs_step_host(copy_back=1): one state per call, nothing overlapped; CUDA events",
+                               "value": cells_total / (ms_single * 1e-3), "ms_per_step": ms_single}}
     else:
         e2e = stepper.time_e2e(pinned, dev, dt, max(3, min(args.steps, 5)), cells_total)
 
@@ -379,34 +510,38 @@ def run_ours(args):
         del dev
         torch.cuda.empty_cache()
         st64 = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis,
-                                      advect_only=case.advect_only, device=local, rank=0, world=1, kernel=args.kernel)
+                                      advect_only=case.advect_only, device=local, rank=0, world=1, kernel=args.kernel,
+                                      sums_of_entry_state=not args.new_state_sums)
         d64 = [torch.from_numpy(faces_to_padded_tiles(x, p, g, np.float64)).cuda() for x in (case.h, case.u1, case.u2)]
         st64.halo_fill(*d64)
         for _ in range(args.warmup):
-            st64.step(*d64, dt)
+            st64.ctx.step(*d64, dt, diag=diag)
         torch.cuda.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         for _ in range(args.steps):
-            st64.step(*d64, dt)
+            st64.ctx.step(*d64, dt, diag=diag)
         ev1.record()
         torch.cuda.synchronize()
         ms64 = ev0.elapsed_time(ev1)
-        r64 = st64.time_stage_kernel(d64, dt, reps=3)
+        r64 = st64.time_stage_kernel(d64, dt, reps=10)
         ach64 = sum(words[a == 0.0] for a in r64["a"]) * 8 * cells_local / (sum(r64["ms"]) * 1e-3) / 1e9
         secondary = {"dtype": "f64", "value": cells_total * args.steps / (ms64 * 1e-3), "unit": UNIT,
-                     "ms_per_step": ms64 / args.steps, "roofline_frac": ach64 / peak, "achieved_GBps": ach64}
+                     "ms_per_step": ms64 / args.steps, "roofline_frac": ach64 / peak, "achieved_GBps": ach64,
+                     "stage_ms": [float(x) for x in r64["ms"]], "fused_sums_us": r64["fused_sums_us"],
+                     "whole_step_frac": 24 * 8 * cells_total / (ms64 / args.steps * 1e-3) / 1e9 / peak}
         del d64, st64
 
-    # ---- CPU baseline on rank 0 (bounded sample of the same workload) --------------------------
+    # ---- CPU baseline on rank 0 (bounded sample of the same workload, same precision) --------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             # about 15 s of CPU work: time one probe step, then size the sample
-            _, _, probe = cpu_run(case, dt, 1, 1)
+            _, _, probe = cpu_run(case, dt, 1, 1, args.dtype)
             nsample = int(max(3, min(300, 15.0 / max(probe, 1e-3))))
-            val, threads, sec = cpu_run(case, dt, nsample, 0)
+            val, threads, sec = cpu_run(case, dt, nsample, 0, args.dtype)
             cpu = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                   "sample": f"{nsample} full fp64 steps of {args.case} C{N} after a warm-up, C + OpenMP oracle ({sec:.1f} s)"}
+                   "sample": f"{nsample} full {args.dtype} steps of {args.case} C{N} after a warm-up, C + OpenMP oracle ({sec:.1f} s)"}
         except Exception as exc:  # pragma: no cover
             cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {exc}"}
 
@@ -415,14 +550,21 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if args.N else "weak", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": f"{args.case} C{N}, SSP-RK3 (3 fused stages + halo) per step, {args.dtype}",
+            "config": {"workload": f"{args.case} C{N}, SSP-RK3 (3 fused stages + halo + mass/energy sums) per step, {args.dtype}",
                        "N": N, "tiles_per_edge": p, "halo": g, "tiles_per_gpu": tc, "parallelism": f"tiles/{world}",
+                       "reductions": ("mass and energy every step: of the new state, summed inside the last stage launch"
+                                      if args.new_state_sums else
+                                      "mass and energy every step: of the state the step starts from, summed inside the first stage launch")
+                                     + ("" if world == 1 else " (inner + rim kernels), then one all-reduce of 4 doubles"),
                        "l2": "state (3 x %.0f MB x 3 buffers per GPU) is larger than L2; no flush needed" %
                              (cells_local * esize / 1e6),
                        "finite": finite},
+            "ms_per_step_without_sums": ms_nosums / args.steps, "diag": d_after,
             "roofline": roofline, "halo": halo, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clk.summary(),
         }
+        if parity is not None:
+            line["parity"] = parity
         if secondary:
             line["fp64"] = secondary
         _emit(line)

@@ -8,9 +8,15 @@
  * Boundary rules
  *   - plain C: pointers, sizes, PODs; no C++ or torch types cross this header;
  *   - every device pointer is caller-owned memory on the context's device;
- *   - every call only ENQUEUES work on the given stream (a cudaStream_t passed as
- *     void*; NULL = the legacy default stream) and never synchronises, except
- *     cs_ctx_create / cs_ctx_destroy / cs_step_host[_batch] which own their synchronisation;
+ *   - the compute calls (cs_halo_fill_*, cs_halo_pack / unpack, cs_rk_stage[_part], cs_step,
+ *     cs_diagnostics[_noalloc]) only ENQUEUE work on the given stream (a cudaStream_t passed as
+ *     void*; NULL = the legacy default stream); they neither synchronise nor allocate.  One
+ *     exception: the first cs_step for a new (h, u, v, dt, diag_out) combination captures and
+ *     instantiates a CUDA graph (creates a stream, allocates graph memory; CS_STEP_GRAPH=0 opts out);
+ *   - the set-up calls synchronise the device and/or allocate: cs_ctx_create, cs_ctx_destroy,
+ *     cs_halo_set_rotation, cs_halo_plan, and cs_step_host[_batch] (which own their copies);
+ *   - every call runs on the context's device and restores the calling thread's current CUDA
+ *     device before it returns;
  *   - return value 0 = success, negative = CS_E_* below; the text of the last
  *     error of a context (or of the calling thread when ctx is NULL) is
  *     cs_last_error();
@@ -63,6 +69,8 @@ extern "C" {
 #define CS_LIM_NONE 0
 #define CS_LIM_MINMOD 1
 #define CS_LIM_MC 2
+#define CS_SUMS_OF_OUTPUT 0      /* cs_rk_stage_part_sums: sums over qout                    */
+#define CS_SUMS_OF_INPUT 1       /*                        sums over qs (the stage input)    */
 #define CS_KERNEL_AUTO 0         /* fastest validated stage kernel                           */
 #define CS_KERNEL_NAIVE 1        /* one thread per cell, global loads only (cross-check)     */
 #define CS_KERNEL_MARCH 2        /* register-marching kernel, direct global loads            */
@@ -87,7 +95,11 @@ typedef struct cs_config {
     int32_t fused_halo;       /* 1: stage kernel also stores boundary cells into the neighbours' edge ghosts  */
                               /*    (no halo launch; corner blocks not refreshed).  Off by default: measured  */
                               /*    slower than the separate 3-microsecond halo launch   */
-    int32_t reserved[3];
+    int32_t sums_of_entry_state; /* 0: cs_step's diag_out = mass / energy of the NEW state (summed inside the last stage
+                                  *    launch); 1: of the state the step STARTS from (summed inside the first stage launch,
+                                  *    where it costs a few instructions per cell and no registers: state n's sums arrive
+                                  *    with step n + 1, and a final cs_diagnostics gives the last state's) */
+    int32_t reserved[2];
     double radius;            /* a      (0 -> 6.37122e6 m)                                   */
     double omega;             /* Omega  (0 -> 7.292e-5 1/s; set advect_only for no rotation) */
     double gravity;           /* g      (0 -> 9.80616 m/s^2)                                 */
@@ -180,7 +192,9 @@ CS_API int cs_rk_stage(cs_ctx* ctx, const void* const q0[3], const void* const q
  * One explicit time step, in place: h, u, v must be halo-filled on entry and are
  * halo-filled on return.  Replaces: step(state, dt) of BASELINE.json's
  * north_star (the solver driver behind deck slide 7; not shipped).
- * diag_out as in cs_rk_stage (values of the new state), may be NULL.
+ * diag_out (device double[2], may be NULL): mass and total energy of the new state, or -- on a context created
+ * with sums_of_entry_state = 1 -- of the state on entry.  Either way they come out of a stage launch, not out of
+ * another pass over the state.
  */
 CS_API int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out, void* stream);
 
@@ -243,6 +257,18 @@ CS_API int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void* co
                      double a, double b, double dt, int part, void* stream);
 
 /*
+ * cs_rk_stage_part that also leaves, in sums_out (device double[2], may be NULL), the mass and total energy summed
+ * over the cells THIS part computes (part 0 + part 1 = the shard; add the two, then add over shards): of the new
+ * values (which = CS_SUMS_OF_OUTPUT) or of the stage input qs at those cells (CS_SUMS_OF_INPUT, much cheaper).  The
+ * sums come out of the stage launch itself: nothing is read twice.  Available for the marching kernel (parts 0, 2) and
+ * the rim kernel (part 1); other variants return CS_E_UNSUPPORTED after enqueuing the stage.  Parts 0 and 1 may
+ * run at the same time on two streams (they use separate scratch); give them separate sums_out.
+ * Replaces: conservation diagnostics named by north_star, for a state sharded with P('tiles') (PY:77-79).
+ */
+CS_API int cs_rk_stage_part_sums(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3],
+                          double a, double b, double dt, int part, int which, double* sums_out, void* stream);
+
+/*
  * Mass and total energy like cs_diagnostics, for callers that cannot allocate device memory and
  * therefore cannot create a cs_ctx: plugin handlers inside a framework that has reserved the GPU
  * for its own allocator (under JAX/XLA preallocation a cudaMalloc from a plugin can fail), and
@@ -253,7 +279,9 @@ CS_API int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void* co
  * tile_count 0 = all) and the output (device double[2]).  radius / gravity 0 select the defaults.
  * Scratch is a fixed static array inside the library (about 128 KB on every GPU that loads it, kept
  * until exit): at most 33,554,432 interior cells per call (C1536 whole sphere: 14,155,776), larger
- * shards return CS_E_INVALID.  The first call on a device resolves the array's address; make that
+ * shards return CS_E_INVALID.  The metric is that of the default equiangular grid: a custom tangent
+ * table (cs_config.tangents) is a context feature and is NOT honoured here.  The calling thread's
+ * current device is restored on return.  The first call on a device resolves the array's address; make that
  * call before any stream capture on that device.  All calls on a device share the array (it keeps
  * the last call's partial sums; the ticket counter is cleared on every call), so calls whose
  * kernels may overlap on the GPU race: serialise them on one stream.
@@ -261,6 +289,14 @@ CS_API int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void* co
 CS_API int cs_diagnostics_noalloc(int dtype, int N, int tiles_per_edge, int halo, int tile_begin, int tile_count,
                                   double radius, double gravity, const void* h, const void* u, const void* v,
                                   const void* hs, double* out, int device, void* stream);
+
+/*
+ * Which stage kernel ran: *last_variant = CS_KERNEL_* of the most recent cs_rk_stage / cs_step launch
+ * (CS_KERNEL_AUTO before the first one), *naive_fallbacks = how many launches a CS_KERNEL_AUTO context had to
+ * send to the one-thread-per-cell kernel (about 4x slower) because the fields were not 16-byte aligned, the row
+ * length was odd or halo < 2.  Either pointer may be NULL.  Replaces: nothing (bookkeeping).
+ */
+CS_API int cs_stage_kernel_info(const cs_ctx* ctx, int32_t* last_variant, int64_t* naive_fallbacks);
 
 /* Number of kernels this library has launched on ctx since creation (bench bookkeeping). */
 CS_API int64_t cs_launch_count(const cs_ctx* ctx);

@@ -14,7 +14,9 @@
  * The product never links or loads this file.
  *
  * Build: make -C oracle   (gcc -O3 -fopenmp -ffp-contract=off; no FMA contraction so that the
- * results track the NumPy oracle to the last bits).
+ * results track the NumPy oracle to the last bits).  -DCSO_REAL=float builds the same source with
+ * the state, the metric tables and the per-cell arithmetic in single precision (set-up and the
+ * conservation sums stay in double): the CPU arm of bench.py in the GPU arm's precision.
  */
 #include <math.h>
 #include <stdint.h>
@@ -25,14 +27,25 @@
 #include <omp.h>
 #endif
 
+#ifndef CSO_REAL
+#define CSO_REAL double
+#endif
+typedef CSO_REAL real;
+#define R_(x) ((real)(x))
+static inline real r_min(real a, real b) { return sizeof(real) == 8 ? (real)fmin(a, b) : (real)fminf((float)a, (float)b); }
+static inline real r_max(real a, real b) { return sizeof(real) == 8 ? (real)fmax(a, b) : (real)fmaxf((float)a, (float)b); }
+static inline real r_abs(real a) { return sizeof(real) == 8 ? (real)fabs(a) : (real)fabsf((float)a); }
+
+int cso_real_bytes(void) { return (int)sizeof(real); }
+
 typedef struct {
     int N, g, M;
     int limiter, rk, advect_only;
     double a, omega, grav, delta;
-    double *sg, *isg, *g11, *g12, *g22, *gi11, *gi12, *gi22;   /* [M*M] */
-    double *fsg;                                               /* [6*M*M] */
-    double *hs;                                                /* [6*M*M] */
-    double *w[14];                                             /* work arrays [6*M*M] */
+    real *sg, *isg, *g11, *g12, *g22, *gi11, *gi12, *gi22;     /* [M*M] */
+    real *fsg;                                                 /* [6*M*M] */
+    real *hs;                                                  /* [6*M*M] */
+    real *w[14];                                               /* work arrays [6*M*M] */
 } cso_ctx;
 
 static const int FR[6][3][3] = {
@@ -78,7 +91,7 @@ static seam_t seam(int f, int e) {
 }
 
 /* Fill the ghosts of h (scalar, may be NULL) and (u, v) (vector pair, may be NULL). */
-void cso_halo_fill(int N, int g, double* h, double* u, double* v) {
+void cso_halo_fill(int N, int g, real* h, real* u, real* v) {
     const int M = N + 2 * g;
     const size_t FS = (size_t)M * M;
     for (int f = 0; f < 6; ++f)
@@ -103,7 +116,7 @@ void cso_halo_fill(int N, int g, double* h, double* u, double* v) {
                     size_t od = f * FS + (size_t)jd * M + id, os = s.fb * FS + (size_t)js * M + is;
                     if (h) h[od] = h[os];
                     if (u) {
-                        double src[2] = {u[os], v[os]}, out[2];
+                        real src[2] = {u[os], v[os]}, out[2];
                         for (int r = 0; r < 2; ++r) {
                             int col = s.S[r][0] != 0 ? 0 : 1;
                             out[r] = s.S[r][col] < 0 ? -src[col] : src[col];
@@ -113,9 +126,9 @@ void cso_halo_fill(int N, int g, double* h, double* u, double* v) {
                 }
         }
     /* cube-vertex blocks: constant extrapolation of the E/W ghost columns in y */
-    double* fields[3] = {h, u, v};
+    real* fields[3] = {h, u, v};
     for (int q = 0; q < 3; ++q) {
-        double* a = fields[q];
+        real* a = fields[q];
         if (!a) continue;
         for (int f = 0; f < 6; ++f)
             for (int d = 0; d < g; ++d)
@@ -130,18 +143,18 @@ void cso_halo_fill(int N, int g, double* h, double* u, double* v) {
 }
 
 cso_ctx* cso_create(int N, int g, int limiter, int rk, int advect_only, double a, double omega, double grav,
-                    const double* axis, const double* tangents /* N */, const double* hs /* [6][M][M] or NULL */) {
+                    const double* axis, const double* tangents /* N */, const real* hs /* [6][M][M] or NULL */) {
     cso_ctx* c = (cso_ctx*)calloc(1, sizeof(cso_ctx));
     const int M = N + 2 * g;
     const size_t FS = (size_t)M * M;
     c->N = N, c->g = g, c->M = M, c->limiter = limiter, c->rk = rk, c->advect_only = advect_only;
     c->a = a, c->omega = omega, c->grav = grav, c->delta = 0.5 * 3.14159265358979323846 / N;
-    double** tabs[] = {&c->sg, &c->isg, &c->g11, &c->g12, &c->g22, &c->gi11, &c->gi12, &c->gi22};
-    for (int k = 0; k < 8; ++k) *tabs[k] = (double*)malloc(FS * sizeof(double));
-    c->fsg = (double*)malloc(6 * FS * sizeof(double));
-    c->hs = (double*)calloc(6 * FS, sizeof(double));
-    if (hs) memcpy(c->hs, hs, 6 * FS * sizeof(double));
-    for (int k = 0; k < 14; ++k) c->w[k] = (double*)calloc(6 * FS, sizeof(double));
+    real** tabs[] = {&c->sg, &c->isg, &c->g11, &c->g12, &c->g22, &c->gi11, &c->gi12, &c->gi22};
+    for (int k = 0; k < 8; ++k) *tabs[k] = (real*)malloc(FS * sizeof(real));
+    c->fsg = (real*)malloc(6 * FS * sizeof(real));
+    c->hs = (real*)calloc(6 * FS, sizeof(real));
+    if (hs) memcpy(c->hs, hs, 6 * FS * sizeof(real));
+    for (int k = 0; k < 14; ++k) c->w[k] = (real*)calloc(6 * FS, sizeof(real));
     double* xt = (double*)malloc(M * sizeof(double));
     for (int I = 0; I < M; ++I) xt[I] = tangents[((I - g) % N + N) % N];
     const double ia2 = 1.0 / (a * a);
@@ -151,16 +164,17 @@ cso_ctx* cso_create(int N, int g, int limiter, int rk, int advect_only, double a
             const double A = 1.0 + X * X, B = 1.0 + Y * Y, rho2 = A + Y * Y, r2inv = 1.0 / rho2;
             const double cc = (a * a) * A * B * (r2inv * r2inv);
             const size_t o = (size_t)j * M + i;
-            c->sg[o] = cc * sqrt(rho2);
-            c->isg[o] = 1.0 / c->sg[o];
-            c->g11[o] = cc * A, c->g12[o] = -(cc * X) * Y, c->g22[o] = cc * B;
-            c->gi11[o] = (rho2 * ia2) / A;
-            c->gi12[o] = ((rho2 * ia2) * (X * Y)) / (A * B);
-            c->gi22[o] = (rho2 * ia2) / B;
+            const double sg = cc * sqrt(rho2);            /* tables are computed in double and stored as real */
+            c->sg[o] = R_(sg);
+            c->isg[o] = R_(1.0 / sg);
+            c->g11[o] = R_(cc * A), c->g12[o] = R_(-(cc * X) * Y), c->g22[o] = R_(cc * B);
+            c->gi11[o] = R_((rho2 * ia2) / A);
+            c->gi12[o] = R_(((rho2 * ia2) * (X * Y)) / (A * B));
+            c->gi22[o] = R_((rho2 * ia2) / B);
             for (int f = 0; f < 6; ++f) {
                 double cf[3];
                 for (int k = 0; k < 3; ++k) cf[k] = axis[0] * FR[f][k][0] + axis[1] * FR[f][k][1] + axis[2] * FR[f][k][2];
-                c->fsg[f * FS + o] = (2.0 * omega) * (cf[0] + cf[1] * X + cf[2] * Y) * cc;
+                c->fsg[f * FS + o] = R_((2.0 * omega) * (cf[0] + cf[1] * X + cf[2] * Y) * cc);
             }
         }
     free(xt);
@@ -169,28 +183,30 @@ cso_ctx* cso_create(int N, int g, int limiter, int rk, int advect_only, double a
 
 void cso_destroy(cso_ctx* c) {
     if (!c) return;
-    double* p[] = {c->sg, c->isg, c->g11, c->g12, c->g22, c->gi11, c->gi12, c->gi22, c->fsg, c->hs};
+    real* p[] = {c->sg, c->isg, c->g11, c->g12, c->g22, c->gi11, c->gi12, c->gi22, c->fsg, c->hs};
     for (int k = 0; k < 10; ++k) free(p[k]);
     for (int k = 0; k < 14; ++k) free(c->w[k]);
     free(c);
 }
 
-static inline double sgn(double x) { return (x > 0.0) - (x < 0.0); }
+static inline real sgn(real x) { return R_((x > R_(0)) - (x < R_(0))); }
 
-static inline double slope(double dm, double dp, int lim) {
-    if (lim == 0) return 0.5 * (dm + dp);
-    const double s = 0.5 * (sgn(dm) + sgn(dp));
-    if (lim == 1) return s * fmin(fabs(dm), fabs(dp));
-    return s * fmin(fmin(2.0 * fabs(dm), 2.0 * fabs(dp)), 0.5 * fabs(dm + dp));
+static inline real slope(real dm, real dp, int lim) {
+    if (lim == 0) return R_(0.5) * (dm + dp);
+    const real s = R_(0.5) * (sgn(dm) + sgn(dp));
+    if (lim == 1) return s * r_min(r_abs(dm), r_abs(dp));
+    return s * r_min(r_min(R_(2) * r_abs(dm), R_(2) * r_abs(dp)), R_(0.5) * r_abs(dm + dp));
 }
 
 /* out = ca * q0 + cb * (qs + dt * L(qs)) on interior cells; qs halo-filled */
-static void stage(cso_ctx* c, const double* h0, const double* u0, const double* v0, const double* h, const double* u,
-                  const double* v, double* ho, double* uo, double* vo, double ca, double cb, double dt) {
+static void stage(cso_ctx* c, const real* h0, const real* u0, const real* v0, const real* h, const real* u,
+                  const real* v, real* ho, real* uo, real* vo, double ca_, double cb_, double dt_) {
     const int N = c->N, g = c->g, M = c->M, lim = c->limiter;
     const size_t FS = (size_t)M * M;
-    double *m1 = c->w[6], *m2 = c->w[7], *c1 = c->w[8], *c2 = c->w[9], *Bn = c->w[10], *sx = c->w[11], *sy = c->w[12];
-    const double rd = 1.0 / c->delta, r2d = 0.5 / c->delta, grav = c->grav;
+    real *m1 = c->w[6], *m2 = c->w[7], *c1 = c->w[8], *c2 = c->w[9], *Bn = c->w[10], *sx = c->w[11], *sy = c->w[12];
+    const real rd = R_(1.0 / c->delta), r2d = R_(0.5 / c->delta), grav = R_(c->grav);
+    /* the convex pair stays convex after rounding to real (a + b == 1 exactly), as in the product */
+    const real cb = R_(cb_), ca = ca_ != 0.0 ? R_(1) - cb : R_(0), dt = R_(dt_);
 #pragma omp parallel for collapse(2) schedule(static)
     for (int f = 0; f < 6; ++f)
         for (int j = 0; j < M; ++j) {
@@ -198,14 +214,14 @@ static void stage(cso_ctx* c, const double* h0, const double* u0, const double* 
             const size_t trow = (size_t)j * M;
             for (int i = 0; i < M; ++i) {
                 const size_t o = row + i, t = trow + i;
-                const double uu = u[o], vv = v[o];
+                const real uu = u[o], vv = v[o];
                 m1[o] = c->sg[t] * uu;
                 m2[o] = c->sg[t] * vv;
-                const double a1 = c->g11[t] * uu + c->g12[t] * vv, a2 = c->g12[t] * uu + c->g22[t] * vv;
+                const real a1 = c->g11[t] * uu + c->g12[t] * vv, a2 = c->g12[t] * uu + c->g22[t] * vv;
                 c1[o] = a1, c2[o] = a2;
-                Bn[o] = grav * (h[o] + c->hs[o]) + 0.5 * (uu * a1 + vv * a2);
-                sx[o] = (i >= 1 && i < M - 1) ? slope(h[o] - h[o - 1], h[o + 1] - h[o], lim) : 0.0;
-                sy[o] = (j >= 1 && j < M - 1) ? slope(h[o] - h[o - M], h[o + M] - h[o], lim) : 0.0;
+                Bn[o] = grav * (h[o] + c->hs[o]) + R_(0.5) * (uu * a1 + vv * a2);
+                sx[o] = (i >= 1 && i < M - 1) ? slope(h[o] - h[o - 1], h[o + 1] - h[o], lim) : R_(0);
+                sy[o] = (j >= 1 && j < M - 1) ? slope(h[o] - h[o - M], h[o + M] - h[o], lim) : R_(0);
             }
         }
 #pragma omp parallel for collapse(2) schedule(static)
@@ -214,21 +230,22 @@ static void stage(cso_ctx* c, const double* h0, const double* u0, const double* 
             const size_t row = f * FS + (size_t)j * M;
             for (int i = g; i < g + N; ++i) {
                 const size_t o = row + i, t = (size_t)j * M + i;
-                double Fm, FE, FW, GN, GS;
-                Fm = 0.5 * (m1[o] + m1[o + 1]);
-                FE = fmax(Fm, 0.0) * (h[o] + 0.5 * sx[o]) + fmin(Fm, 0.0) * (h[o + 1] - 0.5 * sx[o + 1]);
-                Fm = 0.5 * (m1[o - 1] + m1[o]);
-                FW = fmax(Fm, 0.0) * (h[o - 1] + 0.5 * sx[o - 1]) + fmin(Fm, 0.0) * (h[o] - 0.5 * sx[o]);
-                Fm = 0.5 * (m2[o] + m2[o + M]);
-                GN = fmax(Fm, 0.0) * (h[o] + 0.5 * sy[o]) + fmin(Fm, 0.0) * (h[o + M] - 0.5 * sy[o + M]);
-                Fm = 0.5 * (m2[o - M] + m2[o]);
-                GS = fmax(Fm, 0.0) * (h[o - M] + 0.5 * sy[o - M]) + fmin(Fm, 0.0) * (h[o] - 0.5 * sy[o]);
-                const double dh = -(((FE - FW) + (GN - GS)) * rd) * (1.0 / c->sg[t]);
-                double du = 0.0, dv = 0.0;
+                const real Z = R_(0), H = R_(0.5);
+                real Fm, FE, FW, GN, GS;
+                Fm = H * (m1[o] + m1[o + 1]);
+                FE = r_max(Fm, Z) * (h[o] + H * sx[o]) + r_min(Fm, Z) * (h[o + 1] - H * sx[o + 1]);
+                Fm = H * (m1[o - 1] + m1[o]);
+                FW = r_max(Fm, Z) * (h[o - 1] + H * sx[o - 1]) + r_min(Fm, Z) * (h[o] - H * sx[o]);
+                Fm = H * (m2[o] + m2[o + M]);
+                GN = r_max(Fm, Z) * (h[o] + H * sy[o]) + r_min(Fm, Z) * (h[o + M] - H * sy[o + M]);
+                Fm = H * (m2[o - M] + m2[o]);
+                GS = r_max(Fm, Z) * (h[o - M] + H * sy[o - M]) + r_min(Fm, Z) * (h[o] - H * sy[o]);
+                const real dh = -(((FE - FW) + (GN - GS)) * rd) * (R_(1) / c->sg[t]);
+                real du = Z, dv = Z;
                 if (!c->advect_only) {
-                    const double eta = ((c2[o + 1] - c2[o - 1]) - (c1[o + M] - c1[o - M])) * r2d + c->fsg[f * FS + t];
-                    const double T1 = eta * v[o] - (Bn[o + 1] - Bn[o - 1]) * r2d;
-                    const double T2 = -eta * u[o] - (Bn[o + M] - Bn[o - M]) * r2d;
+                    const real eta = ((c2[o + 1] - c2[o - 1]) - (c1[o + M] - c1[o - M])) * r2d + c->fsg[f * FS + t];
+                    const real T1 = eta * v[o] - (Bn[o + 1] - Bn[o - 1]) * r2d;
+                    const real T2 = -eta * u[o] - (Bn[o + M] - Bn[o - M]) * r2d;
                     du = c->gi11[t] * T1 + c->gi12[t] * T2;
                     dv = c->gi12[t] * T1 + c->gi22[t] * T2;
                 }
@@ -241,18 +258,18 @@ static void stage(cso_ctx* c, const double* h0, const double* u0, const double* 
 }
 
 /* nsteps explicit steps in place; h, u, v halo-filled [6][M][M] */
-void cso_step(cso_ctx* c, double* h, double* u, double* v, double dt, int nsteps) {
+void cso_step(cso_ctx* c, real* h, real* u, real* v, double dt, int nsteps) {
     static const double PA[3][3] = {{0, 0, 0}, {0, 0.5, 0}, {0, 0.75, 0}};
     const int ns = c->rk;   /* 1 euler, 2 ssprk2, 3 ssprk3 */
     double ca[3] = {0.0, PA[ns - 1][1], 1.0 - 2.0 / 3.0}, cb[3] = {1.0, 1.0 - PA[ns - 1][1], 2.0 / 3.0};
     if (ns == 2) ca[1] = 0.5, cb[1] = 0.5;
     if (ns == 3) ca[1] = 0.75, cb[1] = 0.25;
-    const size_t bytes = 6 * (size_t)c->M * c->M * sizeof(double);
+    const size_t bytes = 6 * (size_t)c->M * c->M * sizeof(real);
     for (int it = 0; it < nsteps; ++it) {
-        double *qa[3] = {c->w[0], c->w[1], c->w[2]}, *qb[3] = {c->w[3], c->w[4], c->w[5]};
-        const double *ch = h, *cu = u, *cv = v;
+        real *qa[3] = {c->w[0], c->w[1], c->w[2]}, *qb[3] = {c->w[3], c->w[4], c->w[5]};
+        const real *ch = h, *cu = u, *cv = v;
         for (int s = 0; s < ns; ++s) {
-            double** dst = (s % 2 == 0) ? qa : qb;
+            real** dst = (s % 2 == 0) ? qa : qb;
             stage(c, h, u, v, ch, cu, cv, dst[0], dst[1], dst[2], ca[s], cb[s], dt);
             ch = dst[0], cu = dst[1], cv = dst[2];
         }
@@ -260,7 +277,7 @@ void cso_step(cso_ctx* c, double* h, double* u, double* v, double dt, int nsteps
     }
 }
 
-void cso_diagnostics(cso_ctx* c, const double* h, const double* u, const double* v, double* out) {
+void cso_diagnostics(cso_ctx* c, const real* h, const real* u, const real* v, double* out) {
     const int N = c->N, g = c->g, M = c->M;
     const size_t FS = (size_t)M * M;
     double mass = 0.0, energy = 0.0;
@@ -270,10 +287,12 @@ void cso_diagnostics(cso_ctx* c, const double* h, const double* u, const double*
         for (int j = g; j < g + N; ++j)
             for (int i = g; i < g + N; ++i) {
                 const size_t o = f * FS + (size_t)j * M + i, t = (size_t)j * M + i;
-                const double a1 = c->g11[t] * u[o] + c->g12[t] * v[o], a2 = c->g12[t] * u[o] + c->g22[t] * v[o];
-                const double K = 0.5 * (u[o] * a1 + v[o] * a2), w = c->sg[t] * da;
-                mass += w * h[o];
-                energy += w * (h[o] * K + 0.5 * c->grav * h[o] * h[o] + c->grav * h[o] * c->hs[o]);
+                /* always in double, whatever real is */
+                const double hh = h[o], uu = u[o], vv = v[o], hs = c->hs[o];
+                const double a1 = (double)c->g11[t] * uu + (double)c->g12[t] * vv, a2 = (double)c->g12[t] * uu + (double)c->g22[t] * vv;
+                const double K = 0.5 * (uu * a1 + vv * a2), w = (double)c->sg[t] * da;
+                mass += w * hh;
+                energy += w * (hh * K + 0.5 * c->grav * hh * hh + c->grav * hh * hs);
             }
     out[0] = mass, out[1] = energy;
 }

@@ -34,7 +34,7 @@ bool single_device(const cs_ctx* ctx) { return ctx->T == ctx->T_all; }
 
 extern "C" int cs_set_topography(cs_ctx* ctx, const void* hs, void* stream) {
     if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_set_topography: NULL context");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     cudaStream_t s = (cudaStream_t)stream;
     cs_drop_graphs(ctx);
     if (!hs) {
@@ -47,8 +47,8 @@ extern "C" int cs_set_topography(cs_ctx* ctx, const void* hs, void* stream) {
     return cs_launch_halo(ctx, ctx->topo, nullptr, nullptr, 1, s);
 }
 
-extern "C" int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a,
-                                double b, double dt, int part, void* stream) {
+namespace {
+int check_stage_args(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a, int part) {
     if (!ctx || !q0 || !qs || !qout) return cs_fail(ctx, CS_E_INVALID, "cs_rk_stage: NULL argument");
     int rc = check_step_ready(ctx, "cs_rk_stage");
     if (rc) return rc;
@@ -58,17 +58,48 @@ extern "C" int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void
         for (int l = 0; l < 3; ++l)
             if (qout[k] == qs[l]) return cs_fail(ctx, CS_E_INVALID, "cs_rk_stage: qout must not alias qs (stencil input)");
     }
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
-    return cs_launch_stage(ctx, q0, qs, qout, a, b, dt, part, nullptr, (cudaStream_t)stream);
+    return CS_OK;
+}
+}  // namespace
+
+extern "C" int cs_rk_stage_part_sums(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a,
+                                     double b, double dt, int part, int which, double* sums_out, void* stream) {
+    int rc = check_stage_args(ctx, q0, qs, qout, a, part);
+    if (rc) return rc;
+    if (which != CS_SUMS_OF_OUTPUT && which != CS_SUMS_OF_INPUT)
+        return cs_fail(ctx, CS_E_INVALID, "cs_rk_stage_part_sums: which = %d must be CS_SUMS_OF_OUTPUT or CS_SUMS_OF_INPUT", which);
+    CS_ON_DEVICE(ctx, ctx->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    if ((rc = cs_launch_stage(ctx, q0, qs, qout, a, b, dt, part, sums_out, which == CS_SUMS_OF_INPUT, s))) return rc;
+    if (sums_out && !ctx->stage_diag_fused) {
+        if (part == 0 && ctx->n <= 2 * ctx->g) {          // no inner cells at all: their sums are zero
+            CS_CUDA(ctx, cudaMemsetAsync(sums_out, 0, 2 * sizeof(double), s));
+            return CS_OK;
+        }
+        return cs_fail(ctx, CS_E_UNSUPPORTED,
+                       "cs_rk_stage_part_sums: the selected stage kernel cannot sum over part %d of a stage (the marching kernel "
+                       "and the rim kernel can); the stage itself has been enqueued", part);
+    }
+    return CS_OK;
+}
+
+extern "C" int cs_rk_stage_part(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a,
+                                double b, double dt, int part, void* stream) {
+    return cs_rk_stage_part_sums(ctx, q0, qs, qout, a, b, dt, part, CS_SUMS_OF_OUTPUT, nullptr, stream);
 }
 
 extern "C" int cs_rk_stage(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a,
                            double b, double dt, double* diag_out, void* stream) {
-    int rc = cs_rk_stage_part(ctx, q0, qs, qout, a, b, dt, 2, stream);
+    int rc = check_stage_args(ctx, q0, qs, qout, a, 2);
     if (rc) return rc;
+    CS_ON_DEVICE(ctx, ctx->device);
     cudaStream_t s = (cudaStream_t)stream;
+    // the marching kernel produces the conservation sums of qout in the same launch; other variants leave them
+    // to the reduction kernel
+    if ((rc = cs_launch_stage(ctx, q0, qs, qout, a, b, dt, 2, diag_out, 0, s))) return rc;
+    const bool fused = ctx->stage_diag_fused;
     if (!ctx->stage_pushed && (rc = cs_launch_halo(ctx, qout[0], qout[1], qout[2], 3, s))) return rc;
-    if (diag_out) return cs_launch_diag(ctx, qout[0], qout[1], qout[2], diag_out, s);
+    if (diag_out && !fused) return cs_launch_diag(ctx, qout[0], qout[1], qout[2], diag_out, s);
     return CS_OK;
 }
 
@@ -81,18 +112,30 @@ int enqueue_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag
     const int ns = rk_pairs(ctx->cfg.rk, pr);
     void* q0[3] = {h, u, v};
     const void* cur[3] = {h, u, v};
+    bool diag_fused = false;
+    // where the conservation sums come from: the last stage (sums of the new state) or, when the context was created
+    // with sums_of_entry_state, the first stage (sums of the state the step starts from: next to free)
+    const bool entry = ctx->cfg.sums_of_entry_state != 0;
+    const int ksum = entry ? 0 : ns - 1;
     for (int k = 0; k < ns; ++k) {
         // the last stage writes the caller's arrays in place (it reads them point-wise only);
         // a single-stage scheme has nothing else to read from, so it goes through scratch
         void** dst = (k == ns - 1 && ns > 1) ? q0 : (k % 2 == 0 ? ctx->qa : ctx->qb);
-        if ((rc = cs_launch_stage(ctx, q0, cur, dst, pr[k].a, pr[k].b, dt, 2, nullptr, s))) return rc;
+        // the last stage also produces the conservation sums of the new state when its kernel can (K3 fused into K2)
+        if ((rc = cs_launch_stage(ctx, q0, cur, dst, pr[k].a, pr[k].b, dt, 2, k == ksum ? diag_out : nullptr, entry, s))) return rc;
+        if (k == ksum) diag_fused = ctx->stage_diag_fused;
+        if (k == ksum && diag_out && !diag_fused && entry) {
+            // a stage kernel that cannot sum: the reduction kernel on the entry state, before anything overwrites it
+            if ((rc = cs_launch_diag(ctx, h, u, v, diag_out, s))) return rc;
+            diag_fused = true;
+        }
         if (!ctx->stage_pushed && (rc = cs_launch_halo(ctx, dst[0], dst[1], dst[2], 3, s))) return rc;
         for (int c = 0; c < 3; ++c) cur[c] = dst[c];
     }
     if (ns == 1)
         for (int c = 0; c < 3; ++c)
             CS_CUDA(ctx, cudaMemcpyAsync(q0[c], ctx->qa[c], ctx->field_elems * ctx->esize, cudaMemcpyDeviceToDevice, s));
-    if (diag_out) return cs_launch_diag(ctx, h, u, v, diag_out, s);
+    if (diag_out && !diag_fused) return cs_launch_diag(ctx, h, u, v, diag_out, s);
     return CS_OK;
 }
 
@@ -158,13 +201,12 @@ extern "C" int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double
         return cs_fail(ctx, CS_E_INVALID,
                        "cs_step: the context owns %d of %d tiles; drive shards with cs_rk_stage_part + cs_halo_pack/unpack",
                        ctx->T, ctx->T_all);
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     cudaStream_t s = (cudaStream_t)stream;
     // graph replay unless the caller is itself capturing this stream (no nested capture) or opted out
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(s, &cap) != cudaSuccess) cudaGetLastError(), cap = cudaStreamCaptureStatusNone;
-    static const bool want_graph = []() { const char* e = std::getenv("CS_STEP_GRAPH"); return !(e && *e == '0'); }();
-    if (want_graph && cap == cudaStreamCaptureStatusNone) {
+    if (ctx->tune.step_graph && cap == cudaStreamCaptureStatusNone) {
         StepGraph* g = find_or_capture(ctx, h, u, v, dt, diag_out);
         if (!g && ctx->pdl) {                             // a driver that cannot capture programmatic edges: plain edges
             ctx->pdl = false;
@@ -186,7 +228,7 @@ extern "C" int cs_step_host(cs_ctx* ctx, void* h_host, void* u_host, void* v_hos
     int rc = check_step_ready(ctx, "cs_step_host");
     if (rc) return rc;
     if (!single_device(ctx)) return cs_fail(ctx, CS_E_INVALID, "cs_step_host needs a context that owns all tiles");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     const size_t bytes = ctx->field_elems * ctx->esize;
     // device copy of the caller's host state, allocated on first use and kept by the context
     void** d = ctx->host_state;
@@ -256,7 +298,7 @@ extern "C" int cs_step_host_batch(cs_ctx* ctx, int members, void* const* h_host,
     int rc = check_step_ready(ctx, "cs_step_host_batch");
     if (rc) return rc;
     if (!single_device(ctx)) return cs_fail(ctx, CS_E_INVALID, "cs_step_host_batch needs a context that owns all tiles");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     CS_CUDA(ctx, cudaDeviceSynchronize());                // earlier work on other streams may still use the slots
     if ((rc = pipe_setup(ctx))) return rc;
     cs_ctx::HostPipe& p = ctx->pipe;

@@ -28,7 +28,10 @@ struct StageParams {
     const R* xt;              // tan(alpha) at padded face-level index (periodic continuation)
     const R* ainv;            // 1 / (1 + X^2)
     const int4* push;         // [T][4] ghost push descriptors, or nullptr
-    double* partials;         // [blocks][2] mass / energy partial sums, or nullptr
+    double* partials;         // [work items][2] mass / energy partial sums of a stage with fused diagnostics, or nullptr
+    unsigned int* ticket;     // ... its completion counter (zero between launches)
+    double* diag_out;         // ... and where [mass, energy] go
+    int sums_in;              // the sums are those of the stage INPUT (qs) instead of the output
     int n, g, m, p, T, t0;
     int part;                 // 0 inner cells, 1 rim, 2 all
     int advect_only;
@@ -137,11 +140,19 @@ CS_HD TileCoord cs_tile_coord(int tile_global, int p) {
     return c;
 }
 
+// What a stage cell hands back to a caller that also wants the conservation sums: the new values, the
+// topography and the cell's tangents.
+template <typename R>
+struct CellOut {
+    R h, u, v, hs, X, Y;      // new values, topography, tangents
+    R h_in, u_in, v_in;       // the stage input at the same cell
+};
+
 // One interior cell (j, i) of local tile t, everything from global memory.  This is the
 // reference formulation of the stage on the GPU (CS_KERNEL_NAIVE); the fast kernels compute
 // the same expressions with the loads and the derived quantities shared between cells.
 template <typename R, int LIM>
-CS_HD void cs_stage_cell(const StageParams<R>& P, int t, int j, int i) {
+CS_HD void cs_stage_cell(const StageParams<R>& P, int t, int j, int i, CellOut<R>* out = nullptr) {
     const int m = P.m, g = P.g;
     const TileCoord tc = cs_tile_coord(t + P.t0, P.p);
     const R* xt = P.xt + tc.tx * P.n;
@@ -203,4 +214,20 @@ CS_HD void cs_stage_cell(const StageParams<R>& P, int t, int j, int i) {
     P.ho[o] = h1;
     P.uo[o] = u1;
     P.vo[o] = v1;
+    if (out) {
+        out->h = h1, out->u = u1, out->v = v1;
+        out->h_in = hC, out->u_in = uC, out->v_in = vC;
+        out->hs = P.topo ? P.topo[o] : R(0);
+        out->X = MC.X, out->Y = MC.Y;
+    }
+}
+
+// Contribution of one cell to (mass, energy), without the factor delta^2: the all-fp64 per-cell form the
+// reduction kernel uses.
+CS_HD void cs_cell_sums(double X, double Y, double a2, double grav, double h, double u, double v, double hs, double& mass,
+                        double& energy) {
+    const Metric<double> M = cs_metric<double>(X, Y, a2);
+    const Derived<double> D = cs_derive<double>(M, h, u, v, hs, grav);
+    mass += M.sg * h;
+    energy += M.sg * (h * D.K + 0.5 * grav * h * h + grav * h * hs);
 }

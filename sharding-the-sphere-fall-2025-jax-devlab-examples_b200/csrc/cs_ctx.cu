@@ -34,6 +34,13 @@ extern "C" const char* cs_last_error(const cs_ctx* ctx) { return ctx ? ctx->err.
 
 extern "C" int64_t cs_launch_count(const cs_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
+extern "C" int cs_stage_kernel_info(const cs_ctx* ctx, int32_t* last_variant, int64_t* naive_fallbacks) {
+    if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_stage_kernel_info: NULL context");
+    if (last_variant) *last_variant = ctx->last_stage_kernel;
+    if (naive_fallbacks) *naive_fallbacks = ctx->naive_fallbacks;
+    return CS_OK;
+}
+
 namespace {
 
 template <typename R>
@@ -117,6 +124,7 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
     if (cfg->device < 0 || cfg->device >= ndev)
         return cs_fail(nullptr, CS_E_INVALID, "device %d out of range [0, %d)", cfg->device, ndev);
 
+    CS_ON_DEVICE(nullptr, cfg->device);              // the caller's current device is restored on every return path
     cs_ctx* ctx = new cs_ctx();
     ctx->cfg = *cfg;
     ctx->cfg.tangents = nullptr;
@@ -139,7 +147,6 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
         g_thread_error = msg;
         return rc;
     };
-    if (cudaSetDevice(ctx->device) != cudaSuccess) return bail(cs_fail(ctx, CS_E_CUDA, "cudaSetDevice(%d) failed", ctx->device));
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, ctx->device) != cudaSuccess) return bail(cs_fail(ctx, CS_E_CUDA, "cudaGetDeviceProperties failed"));
     if (prop.major != 10)
@@ -163,21 +170,38 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
     }
     if (cudaMalloc(&ctx->topo, bytes) != cudaSuccess) return bail(cs_fail(ctx, CS_E_NOMEM, "cudaMalloc of topography failed"));
     cudaMemsetAsync(ctx->topo, 0, bytes, 0);
-    ctx->partial_cap = 8192;
-    if (cudaMalloc((void**)&ctx->d_partials, (size_t)ctx->partial_cap * 2 * sizeof(double)) != cudaSuccess ||
+    ctx->partial_cap = 65536;   // one (mass, energy) pair per block of the reduction kernel or per work item of a fused stage
+    // three regions of partials and three tickets: [0] stage kernel (whole stage or inner part), [1] rim part (it may
+    // run beside the inner part on another stream), [2] the stand-alone reduction kernel
+    if (cudaMalloc((void**)&ctx->d_partials, 3 * (size_t)ctx->partial_cap * 2 * sizeof(double)) != cudaSuccess ||
         cudaMalloc((void**)&ctx->d_diag, 2 * sizeof(double)) != cudaSuccess ||
-        cudaMalloc((void**)&ctx->d_ticket, sizeof(unsigned int)) != cudaSuccess)
+        cudaMalloc((void**)&ctx->d_ticket, 3 * sizeof(unsigned int)) != cudaSuccess)
         return bail(cs_fail(ctx, CS_E_NOMEM, "cudaMalloc of reduction scratch failed"));
-    cudaMemsetAsync(ctx->d_ticket, 0, sizeof(unsigned int), 0);
+    cudaMemsetAsync(ctx->d_ticket, 0, 3 * sizeof(unsigned int), 0);
     if (cudaDeviceSynchronize() != cudaSuccess) return bail(cs_fail(ctx, CS_E_CUDA, "context set-up failed: %s", cudaGetErrorString(cudaGetLastError())));
     if (const char* e = std::getenv("CS_PDL")) ctx->pdl = *e != '0';
+    // the tuning environment is read here, once: no getenv on any launch path
+    auto env_int = [](const char* name, int dflt) {
+        const char* v = std::getenv(name);
+        return v && *v ? std::atoi(v) : dflt;
+    };
+    CsTuning& tu = ctx->tune;
+    tu.march_prefetch = env_int("CS_MARCH_PREFETCH", tu.march_prefetch);
+    tu.march_rows = env_int("CS_MARCH_ROWS", tu.march_rows);
+    tu.march_vec = env_int("CS_MARCH_VEC", tu.march_vec);
+    tu.march_unit = env_int("CS_MARCH_UNIT", tu.march_unit);
+    tu.reserve_sms = env_int("CS_MARCH_RESERVE_SMS", tu.reserve_sms);
+    tu.tma_ring = env_int("CS_TMA_RING", tu.tma_ring);
+    tu.fused_halo = env_int("CS_FUSED_HALO", tu.fused_halo);
+    tu.step_graph = env_int("CS_STEP_GRAPH", tu.step_graph);
+    tu.fused_diag = env_int("CS_FUSED_DIAG", tu.fused_diag);
     *out = ctx;
     return CS_OK;
 }
 
 extern "C" int cs_ctx_destroy(cs_ctx* ctx) {
     if (!ctx) return CS_OK;
-    cudaSetDevice(ctx->device);
+    CsDeviceGuard guard(ctx->device);
     cudaDeviceSynchronize();
     cs_drop_graphs(ctx);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);

@@ -5,33 +5,12 @@
 // deterministic for a given configuration (no floating-point atomics anywhere).
 #include "cs_internal.cuh"
 #include "cs_cell.cuh"
+#include "cs_reduce.cuh"
 
 namespace {
 
 constexpr int DIAG_THREADS = 256;
 constexpr int DIAG_UNROLL = 4;
-
-__device__ __forceinline__ double warp_sum(double v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-    return v;
-}
-
-// block-level sum of two values; result valid in thread 0
-__device__ __forceinline__ void block_sum2(double& a, double& b) {
-    __shared__ double sa[DIAG_THREADS / 32], sb[DIAG_THREADS / 32];
-    a = warp_sum(a);
-    b = warp_sum(b);
-    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-    if (l == 0) sa[w] = a, sb[w] = b;
-    __syncthreads();
-    if (w == 0) {
-        a = l < DIAG_THREADS / 32 ? sa[l] : 0.0;
-        b = l < DIAG_THREADS / 32 ? sb[l] : 0.0;
-        a = warp_sum(a);
-        b = warp_sum(b);
-    }
-}
 
 template <typename R>
 __global__ void __launch_bounds__(DIAG_THREADS)
@@ -83,28 +62,8 @@ diag_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restric
             }
         }
     }
-    block_sum2(mass, energy);
-    __shared__ bool last;
-    if (threadIdx.x == 0) {
-        partials[2 * blockIdx.x] = mass;
-        partials[2 * blockIdx.x + 1] = energy;
-        __threadfence();
-        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
-    }
-    __syncthreads();
-    if (last) {   // fixed-order final sum by the last block
-        __threadfence();
-        double a = 0.0, b = 0.0;
-        for (int k = threadIdx.x; k < (int)gridDim.x; k += DIAG_THREADS) {
-            a += partials[2 * k];
-            b += partials[2 * k + 1];
-        }
-        block_sum2(a, b);
-        if (threadIdx.x == 0) {
-            out[0] = a, out[1] = b;
-            *ticket = 0;   // ready for the next launch on this stream
-        }
-    }
+    cs_block_sum2<DIAG_THREADS>(mass, energy);
+    cs_finish_partials<DIAG_THREADS>(partials, ticket, blockIdx.x, gridDim.x, mass, energy, out);
 }
 
 }  // namespace
@@ -120,12 +79,12 @@ int cs_launch_diag(cs_ctx* ctx, const void* h, const void* u, const void* v, dou
         diag_kernel<double><<<(int)blocks, DIAG_THREADS, 0, s>>>((const double*)h, (const double*)u, (const double*)v,
                                                                 ctx->has_topo ? (const double*)ctx->topo : nullptr, ctx->d_xt64,
                                                                 ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, rows_per_block, a2,
-                                                                ctx->gravity, darea, ctx->d_partials, ctx->d_ticket, out);
+                                                                ctx->gravity, darea, ctx->d_partials + 4 * (size_t)ctx->partial_cap, ctx->d_ticket + 2, out);
     else
         diag_kernel<float><<<(int)blocks, DIAG_THREADS, 0, s>>>((const float*)h, (const float*)u, (const float*)v,
                                                                ctx->has_topo ? (const float*)ctx->topo : nullptr, ctx->d_xt64,
                                                                ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, rows_per_block, a2,
-                                                               ctx->gravity, darea, ctx->d_partials, ctx->d_ticket, out);
+                                                               ctx->gravity, darea, ctx->d_partials + 4 * (size_t)ctx->partial_cap, ctx->d_ticket + 2, out);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;
@@ -133,6 +92,6 @@ int cs_launch_diag(cs_ctx* ctx, const void* h, const void* u, const void* v, dou
 
 extern "C" int cs_diagnostics(cs_ctx* ctx, const void* h, const void* u, const void* v, double* out, void* stream) {
     if (!ctx || !h || !u || !v || !out) return cs_fail(ctx, CS_E_INVALID, "cs_diagnostics: NULL argument");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     return cs_launch_diag(ctx, h, u, v, out, (cudaStream_t)stream);
 }

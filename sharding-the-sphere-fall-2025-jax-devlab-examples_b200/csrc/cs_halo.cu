@@ -116,20 +116,20 @@ int cs_launch_halo(cs_ctx* ctx, void* h, void* u, void* v, int mask, cudaStream_
 
 extern "C" int cs_halo_fill_scalar(cs_ctx* ctx, void* field, void* stream) {
     if (!ctx || !field) return cs_fail(ctx, CS_E_INVALID, "cs_halo_fill_scalar: NULL argument");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     return cs_launch_halo(ctx, field, nullptr, nullptr, 1, (cudaStream_t)stream);
 }
 
 extern "C" int cs_halo_fill_vector(cs_ctx* ctx, void* u, void* v, void* stream) {
     if (!ctx || !u || !v) return cs_fail(ctx, CS_E_INVALID, "cs_halo_fill_vector: NULL argument");
     if (u == v) return cs_fail(ctx, CS_E_INVALID, "cs_halo_fill_vector: u and v must be distinct arrays");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     return cs_launch_halo(ctx, nullptr, u, v, 2, (cudaStream_t)stream);
 }
 
 extern "C" int cs_halo_fill_state(cs_ctx* ctx, void* h, void* u, void* v, void* stream) {
     if (!ctx || !h || !u || !v) return cs_fail(ctx, CS_E_INVALID, "cs_halo_fill_state: NULL argument");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     return cs_launch_halo(ctx, h, u, v, 3, (cudaStream_t)stream);
 }
 
@@ -154,7 +154,7 @@ extern "C" int cs_halo_table_info(const cs_ctx* ctx, size_t cap, int64_t* dst_of
 
 extern "C" int cs_halo_set_rotation(cs_ctx* ctx, const double* rot, size_t n_ghost) {
     if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_halo_set_rotation: NULL context");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     CS_CUDA(ctx, cudaDeviceSynchronize());
     cs_drop_graphs(ctx);
     if (ctx->d_rot) cudaFree(ctx->d_rot), ctx->d_rot = nullptr;
@@ -193,7 +193,7 @@ int upload_offsets(cs_ctx* ctx, bool send, int64_t** d_off) {
 extern "C" int cs_halo_plan(cs_ctx* ctx, int n_peers, const int32_t* peer_tile_begin, const int32_t* peer_tile_count,
                             int64_t* send_counts, int64_t* recv_counts) {
     if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_halo_plan: NULL context");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     int rc = cs_build_peer_plan(ctx, n_peers, peer_tile_begin, peer_tile_count);
     if (rc) return rc;
     if ((rc = upload_offsets(ctx, true, &ctx->d_send_off))) return rc;
@@ -241,7 +241,7 @@ extern "C" int cs_halo_pack(cs_ctx* ctx, const void* h, const void* u, const voi
     if (!ctx || !h || !sendbuf || (nfields == 3 && (!u || !v))) return cs_fail(ctx, CS_E_INVALID, "cs_halo_pack: NULL argument");
     if (nfields != 1 && nfields != 3) return cs_fail(ctx, CS_E_INVALID, "cs_halo_pack: nfields must be 1 or 3");
     if (ctx->peers.empty()) return cs_fail(ctx, CS_E_INVALID, "cs_halo_pack: call cs_halo_plan first");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     return cs_launch_pack(ctx, h, u, v, nfields, sendbuf, (cudaStream_t)stream);
 }
 
@@ -249,6 +249,6 @@ extern "C" int cs_halo_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u
     if (!ctx || !h || !recvbuf || (nfields == 3 && (!u || !v))) return cs_fail(ctx, CS_E_INVALID, "cs_halo_unpack: NULL argument");
     if (nfields != 1 && nfields != 3) return cs_fail(ctx, CS_E_INVALID, "cs_halo_unpack: nfields must be 1 or 3");
     if (ctx->peers.empty()) return cs_fail(ctx, CS_E_INVALID, "cs_halo_unpack: call cs_halo_plan first");
-    CS_CUDA(ctx, cudaSetDevice(ctx->device));
+    CS_ON_DEVICE(ctx, ctx->device);
     return cs_launch_unpack(ctx, recvbuf, h, u, v, nfields, (cudaStream_t)stream);
 }

@@ -35,8 +35,22 @@ struct StepGraph {            // one captured step, keyed by what is baked into 
     uint64_t stamp = 0;
 };
 
+// Tuning knobs, read from the CS_* environment variables ONCE, when the context is created.
+struct CsTuning {
+    int march_prefetch = 2;      // CS_MARCH_PREFETCH: L2 prefetch distance in rows
+    int march_rows = 0;          // CS_MARCH_ROWS: strip height, 0 = wave-aware heuristic
+    int march_vec = 4;           // CS_MARCH_VEC: fp32 columns per thread (4 | 2)
+    int march_unit = 1;          // CS_MARCH_UNIT: fp64 first-stage variant
+    int reserve_sms = 12;        // CS_MARCH_RESERVE_SMS: SMs left to the exchange stream by a split stage
+    int tma_ring = 6;            // CS_TMA_RING
+    int fused_halo = 1;          // CS_FUSED_HALO: 0 vetoes cfg.fused_halo
+    int step_graph = 1;          // CS_STEP_GRAPH: 0 = cs_step enqueues its launches instead of replaying a graph
+    int fused_diag = 1;          // CS_FUSED_DIAG: 0 = diagnostics of a step by the separate reduction kernel
+};
+
 struct cs_ctx {
     cs_config cfg;
+    CsTuning tune;
     int N = 0, p = 0, n = 0, g = 0, m = 0;
     int T_all = 0, t0 = 0, T = 0;
     int dtype = CS_F64;
@@ -64,6 +78,7 @@ struct cs_ctx {
     int4* d_push = nullptr;                      // [T][4] (dst local tile or -1, dst edge, reverse, code)
     bool push_complete = false;                  // every neighbour tile is local
     bool stage_pushed = false;                   // the last stage launch stored the edge ghosts itself
+    bool stage_diag_fused = false;               // the last stage launch wrote its diag_out itself (K3 fused into K2)
     bool pdl = false;                            // programmatic dependent launch for stage / halo kernels (CS_PDL=1: on)
 
     // sharded exchange
@@ -103,7 +118,31 @@ struct cs_ctx {
 
     mutable std::string err;
     int64_t launches = 0;
+    int last_stage_kernel = CS_KERNEL_AUTO;      // variant of the most recent stage launch (cs_stage_kernel_info)
+    int64_t naive_fallbacks = 0;                 // CS_KERNEL_AUTO launches that had to take the one-thread-per-cell kernel
 };
+
+// Every entry point runs on the context's device and puts the calling thread's current device back on return: a
+// handler thread of another framework must not find its device switched under it.
+struct CsDeviceGuard {
+    int prev = -1, want = -1;
+    cudaError_t err = cudaSuccess;
+    explicit CsDeviceGuard(int device) : want(device) {
+        err = cudaGetDevice(&prev);
+        if (err != cudaSuccess) prev = -1;
+        if (err == cudaSuccess && prev != device) err = cudaSetDevice(device);
+    }
+    ~CsDeviceGuard() {
+        if (prev >= 0 && prev != want) cudaSetDevice(prev);
+    }
+    CsDeviceGuard(const CsDeviceGuard&) = delete;
+    CsDeviceGuard& operator=(const CsDeviceGuard&) = delete;
+};
+
+#define CS_ON_DEVICE(ctx, device)                                                                                  \
+    CsDeviceGuard cs_guard__(device);                                                                              \
+    if (cs_guard__.err != cudaSuccess)                                                                             \
+        return cs_fail(ctx, CS_E_CUDA, "selecting device %d failed: %s", (int)(device), cudaGetErrorString(cs_guard__.err))
 
 int cs_fail(const cs_ctx* ctx, int code, const char* fmt, ...);
 void cs_drop_graphs(cs_ctx* ctx);   // captured steps bake kernel arguments in: drop them when those change
@@ -126,7 +165,8 @@ int cs_build_peer_plan(cs_ctx* ctx, int n_peers, const int32_t* tb, const int32_
 // kernel launchers (cs_halo.cu, cs_stage.cu, cs_diag.cu)
 int cs_launch_halo(cs_ctx* ctx, void* h, void* u, void* v, int nfields_mask, cudaStream_t s);
 int cs_launch_stage(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3],
-                    double a, double b, double dt, int part, double* diag_out, cudaStream_t s);
+                    double a, double b, double dt, int part, double* diag_out, int sums_in, cudaStream_t s);   // sums_in: diag_out gets
+                                                                          // the sums of the stage input instead of its output
 int cs_launch_diag(cs_ctx* ctx, const void* h, const void* u, const void* v, double* out, cudaStream_t s);
 int cs_launch_pack(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* sendbuf,
                    cudaStream_t s);

@@ -16,6 +16,9 @@
 //
 // Limits and rules (also in include/cubesphere.h):
 //   * at most CS_NOALLOC_MAX_CELLS interior cells per call; larger shards are rejected;
+//   * the metric is the default equiangular one (tan() of the cell-centre angles); a context's custom tangent
+//     table is not known here and not honoured;
+//   * the calling thread's current device is restored on return;
 //   * the first call on each device looks up the array's device address
 //     (cudaGetSymbolAddress, with that device current) and remembers it; make that first call
 //     before starting any stream capture on that device;
@@ -115,8 +118,8 @@ diag_noalloc_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* _
         __threadfence();
         double a = 0.0, b = 0.0;
         for (int k = threadIdx.x; k < (int)gridDim.x; k += CS_NOALLOC_THREADS) {
-            a += partials[2 * k];
-            b += partials[2 * k + 1];
+            a += __ldcg(partials + 2 * k);                // written by other blocks: read through L2, not a stale L1 line
+            b += __ldcg(partials + 2 * k + 1);
         }
         na_block_sum2(a, b);
         if (threadIdx.x == 0) out[0] = a, out[1] = b;
@@ -159,8 +162,8 @@ extern "C" int cs_diagnostics_noalloc(int dtype, int N, int tiles_per_edge, int 
                        "cs_diagnostics_noalloc: %lld interior cells exceed the fixed scratch (%lld cells = %d block partials); "
                        "use cs_diagnostics with a context, or reduce per shard",
                        cells, CS_NOALLOC_MAX_CELLS, CS_NOALLOC_MAX_BLOCKS);
-    cudaError_t e = cudaSetDevice(device);
-    if (e != cudaSuccess) return cs_fail(nullptr, CS_E_CUDA, "cs_diagnostics_noalloc: cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    CS_ON_DEVICE(nullptr, device);                       // the caller's current device is put back on return
+    cudaError_t e;
     double* scratch = nullptr;
     int rc = noalloc_setup(device, &scratch);
     if (rc) return rc;

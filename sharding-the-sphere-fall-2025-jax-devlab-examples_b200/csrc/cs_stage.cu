@@ -1,12 +1,14 @@
 // K2 -- fused Runge-Kutta stage:  out = a q0 + b (qs + dt L(qs)).
 #include "cs_internal.cuh"
 #include "cs_cell.cuh"
+#include "cs_reduce.cuh"
 #include "cs_stage_march.cuh"
 #include "cs_stage_tma.cuh"
 
 #include <cstdlib>
 #include <map>
 #include <mutex>
+#include <tuple>
 #include <utility>
 
 namespace {
@@ -31,30 +33,47 @@ stage_naive_kernel(const __grid_constant__ StageParams<R> P) {
 
 // Rim cells only (those within g of a tile edge): what peers' ghosts depend on.  Used for part 1
 // of a split stage, so that the exchange can start while the inner cells are still being computed.
-template <typename R, int LIM>
+// DIAG: the launch also leaves the (mass, energy) sums over the rim cells in P.diag_out (all-fp64 per cell, one
+// partial per block, the last block adds them in index order).
+template <typename R, int LIM, bool DIAG>
 __global__ void __launch_bounds__(256)
 stage_rim_kernel(const __grid_constant__ StageParams<R> P) {
     const int n = P.n, g = P.g;
     const int per_tile = n * n - (n - 2 * g) * (n - 2 * g);
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= per_tile) return;
-    int j, i;
-    if (idx < 2 * g * n) {            // bottom and top g rows, full width
-        const int r = idx / n;
-        i = idx - r * n;
-        j = r < g ? r : n - 2 * g + r;
-    } else {                          // left and right g columns of the remaining rows
-        const int r = idx - 2 * g * n;
-        const int jj = r / (2 * g), c = r - jj * (2 * g);
-        j = g + jj;
-        i = c < g ? c : n - 2 * g + c;
+    double mass = 0.0, energy = 0.0;
+    if (idx < per_tile) {
+        int j, i;
+        if (idx < 2 * g * n) {            // bottom and top g rows, full width
+            const int r = idx / n;
+            i = idx - r * n;
+            j = r < g ? r : n - 2 * g + r;
+        } else {                          // left and right g columns of the remaining rows
+            const int r = idx - 2 * g * n;
+            const int jj = r / (2 * g), c = r - jj * (2 * g);
+            j = g + jj;
+            i = c < g ? c : n - 2 * g + c;
+        }
+        if constexpr (DIAG) {
+            CellOut<R> o;
+            cs_stage_cell<R, LIM>(P, blockIdx.y, j, i, &o);
+            if (P.sums_in)
+                cs_cell_sums((double)o.X, (double)o.Y, (double)P.a2, (double)P.grav, (double)o.h_in, (double)o.u_in, (double)o.v_in,
+                             (double)o.hs, mass, energy);
+            else
+                cs_cell_sums((double)o.X, (double)o.Y, (double)P.a2, (double)P.grav, (double)o.h, (double)o.u, (double)o.v,
+                             (double)o.hs, mass, energy);
+        } else {
+            cs_stage_cell<R, LIM>(P, blockIdx.y, j, i);
+        }
     }
-    cs_stage_cell<R, LIM>(P, blockIdx.y, j, i);
-}
-
-int env_int(const char* name, int dflt) {
-    const char* v = std::getenv(name);
-    return v && *v ? std::atoi(v) : dflt;
+    if constexpr (DIAG) {
+        const double w = (double)P.darea;
+        mass *= w, energy *= w;
+        cs_block_sum2<256>(mass, energy);
+        cs_finish_partials<256>(P.partials, P.ticket, blockIdx.y * gridDim.x + blockIdx.x, gridDim.x * gridDim.y, mass, energy,
+                                P.diag_out);
+    }
 }
 
 template <typename R>
@@ -68,7 +87,10 @@ StageParams<R> make_params(cs_ctx* ctx, const void* const q0[3], const void* con
     P.xt = (const R*)ctx->d_xt;
     P.ainv = (const R*)ctx->d_ainv;
     P.push = nullptr;        // set by the marching launcher when the halo is fused into the stage
-    P.partials = nullptr;
+    P.partials = nullptr;    // ... when the conservation sums are fused into the stage
+    P.ticket = nullptr;
+    P.diag_out = nullptr;
+    P.sums_in = 0;
     P.n = ctx->n, P.g = ctx->g, P.m = ctx->m, P.p = ctx->p, P.T = ctx->T, P.t0 = ctx->t0;
     P.part = part;
     P.advect_only = ctx->cfg.advect_only;
@@ -99,10 +121,19 @@ int launch_naive(cs_ctx* ctx, const StageParams<R>& P, cudaStream_t s) {
 }
 
 template <typename R, int LIM>
-int launch_rim(cs_ctx* ctx, const StageParams<R>& P, cudaStream_t s) {
+int launch_rim(cs_ctx* ctx, const StageParams<R>& P, double* diag_out, int sums_in, cudaStream_t s) {
     const int per_tile = P.n * P.n - (P.n - 2 * P.g) * (P.n - 2 * P.g);
     dim3 grid((per_tile + 255) / 256, P.T);
-    stage_rim_kernel<R, LIM><<<grid, 256, 0, s>>>(P);
+    if (diag_out && (int64_t)grid.x * grid.y <= ctx->partial_cap) {
+        // the rim may run beside the inner kernel of the same stage on another stream: its own partials and ticket
+        StageParams<R> Q = P;
+        Q.partials = ctx->d_partials + 2 * (size_t)ctx->partial_cap, Q.ticket = ctx->d_ticket + 1, Q.diag_out = diag_out;
+        Q.sums_in = sums_in;
+        stage_rim_kernel<R, LIM, true><<<grid, 256, 0, s>>>(Q);
+        ctx->stage_diag_fused = true;
+    } else {
+        stage_rim_kernel<R, LIM, false><<<grid, 256, 0, s>>>(P);
+    }
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;
@@ -116,15 +147,15 @@ template <typename Kernel>
 MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m, int T, int lo, int hi, size_t smem) {
     MarchGeom G;
     G.xlo = G.ylo = lo, G.xhi = G.yhi = hi;
-    G.prefetch = env_int("CS_MARCH_PREFETCH", 2);
+    G.prefetch = ctx->tune.march_prefetch;
     G.ngroups = m / V;
     G.grp0 = (lo + g) / V;
     const int grp_last = (hi - 1 + g) / V;
     G.nchunks = (grp_last - G.grp0 + 1 + CS_MARCH_OUT_LANES - 1) / CS_MARCH_OUT_LANES;
-    static std::map<std::pair<const void*, size_t>, int> occupancy;      // per kernel instantiation and smem size
+    static std::map<std::tuple<int, const void*, size_t>, int> occupancy;  // per device, kernel instantiation and smem size
     static std::mutex occupancy_mutex;                                      // contexts may be driven from several host threads
     std::lock_guard<std::mutex> lock(occupancy_mutex);
-    const auto key = std::make_pair(reinterpret_cast<const void*>(kernel), smem);
+    const auto key = std::make_tuple(ctx->device, reinterpret_cast<const void*>(kernel), smem);
     auto it = occupancy.find(key);
     if (it == occupancy.end()) {
         int bps = 1;
@@ -137,7 +168,7 @@ MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m,
     const int blocks_per_sm = it->second;
     // the inner part of a split stage (lo > 0) shares the GPU with the rim / pack / NCCL kernels of the side
     // stream: leave them a few SMs, otherwise the displaced warps form a second wave
-    const int reserve = lo > 0 ? env_int("CS_MARCH_RESERVE_SMS", 12) : 0;
+    const int reserve = lo > 0 ? ctx->tune.reserve_sms : 0;
     const int sms = ctx->num_sms - reserve > 8 ? ctx->num_sms - reserve : ctx->num_sms;
     const long long slots = (long long)sms * blocks_per_sm * (CS_MARCH_THREADS / 32);
     const int span = hi - lo;
@@ -150,7 +181,7 @@ MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m,
         const double cost = (double)waves * (r + 5);
         if (cost < best_cost) best_cost = cost, best_rows = r;
     }
-    G.rows = env_int("CS_MARCH_ROWS", best_rows);
+    G.rows = ctx->tune.march_rows > 0 ? ctx->tune.march_rows : best_rows;
     if (G.rows < 1) G.rows = 1;
     G.nstrips = (span + G.rows - 1) / G.rows;
     G.nitems = G.nchunks * G.nstrips * T;
@@ -159,15 +190,34 @@ MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m,
 }
 
 template <typename R, int V, int LIM, int MINB>
-int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_t s) {
+int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* diag_out, int sums_in, cudaStream_t s) {
     const MarchGeom G = march_geometry(ctx, stage_march_kernel<R, V, LIM, MINB, false>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
     const int warps = CS_MARCH_THREADS / 32;
     // First stage, (a, b) = (0, 1): a variant compiled without q0 and without the multiplications by b.  11 % fewer
     // instructions in both precisions, but only fp64 gains (169 -> 154 us at C1536); the fp32 build of it is
     // 7 % SLOWER than the general kernel (87 vs 81 us: a different schedule, not fewer stalls), so fp32 does not use it.
-    static const bool unit_variant = env_int("CS_MARCH_UNIT", 1) != 0;
+    const bool unit_variant = ctx->tune.march_unit != 0;
     const dim3 grid((G.nitems + warps - 1) / warps), block(CS_MARCH_THREADS);
-    if (P.push) {
+    if (diag_out && !P.push && ctx->tune.fused_diag && G.nitems <= ctx->partial_cap) {
+        // last stage of a step: the conservation sums of the output come out of the same launch (K3 fused into K2)
+        // ... or, for a first stage, those of its input (the state the step starts from), which cost next to nothing
+        StageParams<R> Q = P;
+        Q.partials = ctx->d_partials, Q.ticket = ctx->d_ticket, Q.diag_out = diag_out, Q.sums_in = sums_in;
+        if (!sums_in) {
+            CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, false, 1>, grid, block, 0, s, ctx->pdl, Q, G));
+        } else {
+            bool launched = false;
+            if constexpr (sizeof(R) == 8) {
+                if (unit_variant && P.a == R(0) && P.b == R(1)) {
+                    CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, true, 2>, grid, block, 0, s, ctx->pdl, Q, G));
+                    launched = true;
+                }
+            }
+            if (!launched)
+                CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, false, 2>, grid, block, 0, s, ctx->pdl, Q, G));
+        }
+        ctx->stage_diag_fused = true;
+    } else if (P.push) {
         CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, true>, grid, block, 0, s, ctx->pdl, P, G));
     } else {
         bool launched = false;
@@ -188,17 +238,12 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStrea
 template <typename R, int V, int LIM, int MINB>
 int launch_tma(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_t s) {
     const int warps = CS_MARCH_THREADS / 32;
-    int ring = env_int("CS_TMA_RING", 6);
+    int ring = ctx->tune.tma_ring;
     ring = ring < 4 ? 4 : ring > CS_TMA_MAX_RING ? CS_TMA_MAX_RING : ring;
     const int narr = 3 + (P.a != R(0) ? 3 : 0) + (P.topo ? 1 : 0);
     const size_t smem = (size_t)warps * ((size_t)ring * narr * cs_tma_astride<R, V>() + CS_TMA_MAX_RING * 8);
-    static size_t configured = 0;     // per instantiation
-    static std::mutex configured_mutex;
-    std::lock_guard<std::mutex> lock(configured_mutex);
-    if (smem > configured) {
-        CS_CUDA(ctx, cudaFuncSetAttribute(stage_tma_kernel<R, V, LIM, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    // the attribute is per device (and per instantiation): set it on every launch, it costs about a microsecond
+    CS_CUDA(ctx, cudaFuncSetAttribute(stage_tma_kernel<R, V, LIM, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const MarchGeom G = march_geometry(ctx, stage_tma_kernel<R, V, LIM, MINB>, V, P.n, P.g, P.m, P.T, lo, hi, smem);
     stage_tma_kernel<R, V, LIM, MINB><<<(G.nitems + warps - 1) / warps, CS_MARCH_THREADS, smem, s>>>(P, G, ring);
     ctx->launches++;
@@ -209,10 +254,17 @@ int launch_tma(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, cudaStream_
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 template <typename R, int LIM>
-int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
-    const int n = P.n, g = P.g;
+int launch_lim(cs_ctx* ctx, const StageParams<R>& P0, int part, double* diag_out, int sums_in, cudaStream_t s) {
+    const int n = P0.n, g = P0.g;
     ctx->stage_pushed = false;
-    if (part == 1) return launch_rim<R, LIM>(ctx, P, s);
+    ctx->stage_diag_fused = false;
+    StageParams<R> P = P0;
+    if (n <= 2 * g && part != 2) {
+        // a tile this small has no inner cells: every cell is within g of an edge, so the rim is the whole tile
+        if (part == 0) return CS_OK;
+        part = 2, P.part = 2;
+    }
+    if (part == 1) return launch_rim<R, LIM>(ctx, P, diag_out, sums_in, s);
     const int lo = part == 0 ? g : 0, hi = part == 0 ? n - g : n;
     if (hi <= lo) return CS_OK;
     int variant = ctx->cfg.kernel;
@@ -220,16 +272,19 @@ int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
                 aligned16(P.h0) && aligned16(P.u0) && aligned16(P.v0) && aligned16(P.topo);
     const bool can_march = ok16 && g >= 2 && (P.m % 2) == 0 && ((size_t)P.m * P.m * sizeof(R)) % 16 == 0;
     const bool can_tma = can_march && ((size_t)P.m * sizeof(R)) % 16 == 0;
-    if (variant == CS_KERNEL_AUTO) variant = can_march ? CS_KERNEL_MARCH : CS_KERNEL_NAIVE;
+    if (variant == CS_KERNEL_AUTO) {
+        variant = can_march ? CS_KERNEL_MARCH : CS_KERNEL_NAIVE;
+        if (!can_march) ctx->naive_fallbacks++;       // visible through cs_stage_kernel_info: a 4x slower path
+    }
+    ctx->last_stage_kernel = variant;
     if (variant == CS_KERNEL_MARCH && !can_march)
         return cs_fail(ctx, CS_E_INVALID, "the marching stage kernel needs 16-byte aligned fields, halo >= 2 and an even row length");
     if (variant == CS_KERNEL_TMA && !can_tma)
         return cs_fail(ctx, CS_E_INVALID, "the TMA stage kernel needs 16-byte aligned fields and rows, and halo >= 2");
     if (variant == CS_KERNEL_NAIVE) return launch_naive<R, LIM>(ctx, P, s);
     if (variant == CS_KERNEL_TMA) {
-        const int vec = env_int("CS_MARCH_VEC", 0);
         if constexpr (sizeof(R) == 4) {
-            if (vec != 2 && P.m % 4 == 0) return launch_tma<R, 4, LIM, 2>(ctx, P, lo, hi, s);
+            if (ctx->tune.march_vec != 2 && P.m % 4 == 0) return launch_tma<R, 4, LIM, 2>(ctx, P, lo, hi, s);
             return launch_tma<R, 2, LIM, 4>(ctx, P, lo, hi, s);
         } else {
             return launch_tma<R, 2, LIM, 2>(ctx, P, lo, hi, s);
@@ -237,36 +292,35 @@ int launch_lim(cs_ctx* ctx, const StageParams<R>& P, int part, cudaStream_t s) {
     }
     StageParams<R> Q = P;
     ctx->stage_pushed = false;
-    if (part == 2 && ctx->cfg.fused_halo && ctx->push_complete && ctx->d_push && !ctx->d_rot && env_int("CS_FUSED_HALO", 1)) {
+    if (part == 2 && ctx->cfg.fused_halo && ctx->push_complete && ctx->d_push && !ctx->d_rot && ctx->tune.fused_halo) {
         Q.push = ctx->d_push;
         ctx->stage_pushed = true;   // the caller can skip the ghost-fill launch (corner blocks are not refreshed)
     }
     // fp32: four columns per thread (one 16-byte access per row and variable) when rows allow it, else two;
     // fp64: two.  CS_MARCH_VEC=2 forces the two-column fp32 variant (tuning aid).
     if constexpr (sizeof(R) == 4) {
-        if (env_int("CS_MARCH_VEC", 4) == 4 && P.m % 4 == 0) return launch_march<R, 4, LIM, 2>(ctx, Q, lo, hi, s);
-        return launch_march<R, 2, LIM, 4>(ctx, Q, lo, hi, s);
+        if (ctx->tune.march_vec == 4 && P.m % 4 == 0) return launch_march<R, 4, LIM, 2>(ctx, Q, lo, hi, diag_out, sums_in, s);
+        return launch_march<R, 2, LIM, 4>(ctx, Q, lo, hi, diag_out, sums_in, s);
     } else {
-        return launch_march<R, 2, LIM, 2>(ctx, Q, lo, hi, s);
+        return launch_march<R, 2, LIM, 2>(ctx, Q, lo, hi, diag_out, sums_in, s);
     }
 }
 
 template <typename R>
 int launch_typed(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a, double b,
-                 double dt, int part, double* diag_out, cudaStream_t s) {
+                 double dt, int part, double* diag_out, int sums_in, cudaStream_t s) {
     StageParams<R> P = make_params<R>(ctx, q0, qs, qout, a, b, dt, part);
-    (void)diag_out;
     switch (ctx->cfg.limiter) {
-        case CS_LIM_NONE: return launch_lim<R, CS_LIM_NONE>(ctx, P, part, s);
-        case CS_LIM_MINMOD: return launch_lim<R, CS_LIM_MINMOD>(ctx, P, part, s);
-        default: return launch_lim<R, CS_LIM_MC>(ctx, P, part, s);
+        case CS_LIM_NONE: return launch_lim<R, CS_LIM_NONE>(ctx, P, part, diag_out, sums_in, s);
+        case CS_LIM_MINMOD: return launch_lim<R, CS_LIM_MINMOD>(ctx, P, part, diag_out, sums_in, s);
+        default: return launch_lim<R, CS_LIM_MC>(ctx, P, part, diag_out, sums_in, s);
     }
 }
 
 }  // namespace
 
 int cs_launch_stage(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3], double a, double b,
-                    double dt, int part, double* diag_out, cudaStream_t s) {
-    if (ctx->dtype == CS_F64) return launch_typed<double>(ctx, q0, qs, qout, a, b, dt, part, diag_out, s);
-    return launch_typed<float>(ctx, q0, qs, qout, a, b, dt, part, diag_out, s);
+                    double dt, int part, double* diag_out, int sums_in, cudaStream_t s) {
+    if (ctx->dtype == CS_F64) return launch_typed<double>(ctx, q0, qs, qout, a, b, dt, part, diag_out, sums_in, s);
+    return launch_typed<float>(ctx, q0, qs, qout, a, b, dt, part, diag_out, sums_in, s);
 }

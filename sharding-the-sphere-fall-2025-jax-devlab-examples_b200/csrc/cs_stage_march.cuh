@@ -13,6 +13,8 @@
 // `rows`, 2 of 32 lanes), most of which hits L2.
 #pragma once
 
+#include <type_traits>
+
 #include "cs_cell.cuh"
 
 struct MarchGeom {
@@ -70,6 +72,7 @@ template <typename R, int V>
 struct RowDerived {
     R m1[V], m2[V], c1[V], c2[V], Bn[V];
     R isg[V], q[V], fsg[V];   // 1/sqrt(G), rho^2/a^2, f sqrt(G): only used when the row is the output row
+    R sg[V], cc[V];           // sqrt(G) and a^2 A B / rho^4: read by the fused diagnostics only (dead otherwise)
 };
 
 // Half of the limited slope (what the face states need): scaling by 2 is exact, so
@@ -116,11 +119,25 @@ struct MarchConst {
     R kq, kisg, kf2;   // kf2 = kf * cf[2]
 };
 
+// Conservation sums of the stage INPUT (SUMS == 2), taken where the row is derived: sqrt(G) h and
+// sqrt(G) h (Bn - g h / 2) = sqrt(G) h (K + g h / 2 + g hs) are two multiplications and one FMA away from values the
+// derivation has in hand anyway, and nothing has to be kept for later.  `count` says whether this row belongs to the
+// warp's own output rows (every row is derived by two strips, and by none for its ghost rows); om masks the columns.
+struct NoSums {};
 template <typename R, int V>
+struct InSums {
+    const bool (&om)[V];
+    bool count;
+    double& mass;
+    double& energy;
+};
+
+template <typename R, int V, typename SUMS = NoSums>
 __device__ __forceinline__ void march_derive(const StageParams<R>& P, const MarchConst<R, V>& K, R Y, R ay,
                                              const R (&h)[V], const R (&u)[V], const R (&v)[V], const R (&hs)[V],
-                                             RowDerived<R, V>& D) {
+                                             RowDerived<R, V>& D, const SUMS& sums = SUMS()) {
     const R Y2 = Y * Y, B = R(1) + Y2, ayk = ay * K.kisg, cfy = K.kf2 * Y;
+    R pm = R(0), pe = R(0);
 #pragma unroll
     for (int c = 0; c < V; ++c) {
         const R rho2 = K.X[c] * K.X[c] + B;
@@ -139,7 +156,41 @@ __device__ __forceinline__ void march_derive(const StageParams<R>& P, const Marc
         D.q[c] = rho2 * K.kq;
         D.isg[c] = (rho2 * rho) * (K.ax[c] * ayk);          // b dt / delta * rho^3 / (a^2 A B)
         D.fsg[c] = (K.cfx[c] + cfy) * cc;
+        D.sg[c] = sg;
+        D.cc[c] = cc;
+        if constexpr (!std::is_same<SUMS, NoSums>::value) {
+            const R w = sg * h[c];
+            if (sums.om[c]) pm += w, pe += w * (D.Bn[c] - (R(0.5) * P.grav) * h[c]);
+        }
     }
+    if constexpr (!std::is_same<SUMS, NoSums>::value) {
+        // the row's V cells are added in the state's precision, the running sums are kept in fp64
+        if (sums.count) sums.mass += (double)pm, sums.energy += (double)pe;
+    }
+}
+
+// Fused conservation sums (K3 inside the last stage of a step): mass sqrt(G) h and energy
+// sqrt(G) h (K + g h / 2 + g hs) of the V freshly computed cells of one row, from values the thread already
+// holds.  Returned without the constant factors (delta^2, and 1/2 for the energy), which the caller applies once
+// per thread.  2 K = u_i u^i = cc (A u^2 - 2 X Y u v + B v^2).  Arithmetic in the state's precision per cell, the
+// row's V cells are added in that precision and the running sums are kept in fp64.
+template <typename R, int V>
+__device__ __forceinline__ void march_row_diag(const StageParams<R>& P, const MarchConst<R, V>& K, const RowDerived<R, V>& D,
+                                               R Y, const R (&h)[V], const R (&u)[V], const R (&v)[V], const R (&hs)[V],
+                                               const bool (&om)[V], double& mass, double& energy2) {
+    const R a2B = P.a2 * (R(1) + Y * Y), a2Y2 = (P.a2 + P.a2) * Y;
+    R pm = R(0), pe = R(0);
+#pragma unroll
+    for (int c = 0; c < V; ++c) {
+        const R quad = K.a2A[c] * (u[c] * u[c]) - (a2Y2 * K.X[c]) * (u[c] * v[c]) + a2B * (v[c] * v[c]);
+        const R k2 = (D.cc[c] * P.ia2) * quad;                                   // 2 K
+        const R col = k2 + P.grav * (h[c] + (hs[c] + hs[c]));                    // 2 (K + g h / 2 + g hs)
+        const R w = D.sg[c] * h[c];
+        pm += om[c] ? w : R(0);                                                  // halo lanes and ghost columns do not count
+        pe += om[c] ? w * col : R(0);
+    }
+    mass += (double)pm;
+    energy2 += (double)pe;
 }
 
 // Fused halo: a freshly computed boundary cell is also stored into the ghost cell of the neighbouring
@@ -244,7 +295,10 @@ __device__ __forceinline__ void march_row_update(const StageParams<R>& P, const 
     }
 }
 
-template <typename R, int V, int LIM, int MINB, bool PUSH, bool UNIT = false>
+// SUMS: 0 = none; 1 = the launch also leaves mass / energy of its OUTPUT cells in P.diag_out (K3 fused into K2, new-state
+// semantics; costs registers and ~16 instructions per cell); 2 = of its INPUT cells (taken in march_derive, ~6
+// instructions per cell and no registers: the cheap way to monitor conservation, one stage behind).
+template <typename R, int V, int LIM, int MINB, bool PUSH, bool UNIT = false, int SUMS = 0>
 __global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
 stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant__ MarchGeom G) {
     const int lane = threadIdx.x & 31;
@@ -315,6 +369,7 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     const int J0 = j0 + g, J1 = j1 + g;
     R hc[V], hp[V], nh[V], uc[V], vc[V], nu[V], nv[V], nt[V];
     R c1m[V], Bnm[V], Gs[V], syc[V];
+    double dmass = 0.0, denergy2 = 0.0;                   // SUMS: this thread's share of the conservation sums
     RowDerived<R, V> Dc;
     R Yc = yt[J0], ayc = ayt[J0];                         // tan(beta) and 1/(1+Y^2) of the current row
     R Yn = yt[J0 + 1], ayn = ayt[J0 + 1];                 // ... and of the next one (loaded a row ahead)
@@ -342,7 +397,8 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
         IO::ld(P.vq + tbase + (unsigned)(J0 + 1) * m, nv);
         RowDerived<R, V> Dm;
         march_derive<R, V>(P, K, yt[J0 - 1], ayt[J0 - 1], hm1, um, vm, tm, Dm);
-        march_derive<R, V>(P, K, Yc, ayc, hc, uc, vc, tcur, Dc);
+        if constexpr (SUMS == 2) march_derive<R, V>(P, K, Yc, ayc, hc, uc, vc, tcur, Dc, InSums<R, V>{om, true, dmass, denergy2});
+        else march_derive<R, V>(P, K, Yc, ayc, hc, uc, vc, tcur, Dc);
 #pragma unroll
         for (int c = 0; c < V; ++c) {
             const R sym = march_half_slope<R, LIM>(hm1[c] - hmm[c], hc[c] - hm1[c]);
@@ -388,7 +444,8 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
 
         // row J+1: derived quantities, y-slope and the north-face flux of row J
         const R Yn2 = yt[min(J + 2, m - 1)], ayn2 = ayt[min(J + 2, m - 1)];
-        march_derive<R, V>(P, K, Yn, ayn, hp, nu, nv, nt, Dnext);
+        if constexpr (SUMS == 2) march_derive<R, V>(P, K, Yn, ayn, hp, nu, nv, nt, Dnext, InSums<R, V>{om, J + 1 < J1, dmass, denergy2});
+        else march_derive<R, V>(P, K, Yn, ayn, hp, nu, nv, nt, Dnext);
         R dG[V];
 #pragma unroll
         for (int c = 0; c < V; ++c) {
@@ -409,6 +466,13 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
 #pragma unroll
             for (int c = 0; c < V; ++c)
                 if (om[c]) P.ho[oJ + c] = oh[c], P.uo[oJ + c] = ou[c], P.vo[oJ + c] = ov[c];
+        }
+        if constexpr (SUMS == 1) {
+            R hsJ[V];
+#pragma unroll
+            for (int c = 0; c < V; ++c) hsJ[c] = R(0);
+            if (has_topo) IO::ld(P.topo + oJ, hsJ);       // row J again: it was loaded two rows ago and sits in L1 / L2
+            march_row_diag<R, V>(P, K, Dcur, Yc, oh, ou, ov, hsJ, om, dmass, denergy2);
         }
         if constexpr (PUSH) {
             const int j = J - g;
@@ -453,4 +517,41 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
         row(Dn, Dc, J + 1);
     }
     if (J < J1) row(Dc, Dn, J);
+
+    if constexpr (SUMS != 0) {
+        // one (mass, energy) partial per work item; the warp that takes the last ticket adds the partials in index
+        // order, so the result does not depend on which warp finishes when (no floating-point atomics)
+        // SUMS == 1 carries twice the energy density, SUMS == 2 the density itself
+        double pm = dmass * (double)P.darea, pe = denergy2 * ((SUMS == 1 ? 0.5 : 1.0) * (double)P.darea);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            pm += __shfl_down_sync(0xffffffffu, pm, o);
+            pe += __shfl_down_sync(0xffffffffu, pe, o);
+        }
+        unsigned int ticket = 0;
+        if (lane == 0) {
+            P.partials[2 * item] = pm;
+            P.partials[2 * item + 1] = pe;
+            __threadfence();
+            ticket = atomicAdd(P.ticket, 1u);
+        }
+        ticket = __shfl_sync(0xffffffffu, ticket, 0);
+        if (ticket == (unsigned int)G.nitems - 1u) {
+            __threadfence();
+            double a = 0.0, b = 0.0;
+            for (int k = lane; k < G.nitems; k += 32) {
+                a += __ldcg(P.partials + 2 * k);          // other warps wrote these: read through L2, never a stale L1 line
+                b += __ldcg(P.partials + 2 * k + 1);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                a += __shfl_down_sync(0xffffffffu, a, o);
+                b += __shfl_down_sync(0xffffffffu, b, o);
+            }
+            if (lane == 0) {
+                P.diag_out[0] = a, P.diag_out[1] = b;
+                *P.ticket = 0;                            // ready for the next launch on this stream
+            }
+        }
+    }
 }

@@ -15,6 +15,7 @@ LIB_PATH = PKG_ROOT / "lib" / "libcubesphere_b200.so"
 CS_ABI_VERSION = 1
 CS_OK, CS_E_INVALID, CS_E_UNSUPPORTED, CS_E_CUDA, CS_E_NOMEM = 0, -1, -2, -3, -4
 CS_F32, CS_F64 = 0, 1
+CS_SUMS_OF_OUTPUT, CS_SUMS_OF_INPUT = 0, 1
 RK_IDS = {"euler": 1, "ssprk2": 2, "ssprk3": 3}
 LIMITER_IDS = {"none": 0, "minmod": 1, "mc": 2}
 KERNEL_IDS = {"auto": 0, "naive": 1, "march": 2, "tma": 3}
@@ -26,7 +27,7 @@ class CsConfig(C.Structure):
         ("abi_version", C.c_int32), ("N", C.c_int32), ("tiles_per_edge", C.c_int32), ("halo", C.c_int32),
         ("dtype", C.c_int32), ("rk", C.c_int32), ("limiter", C.c_int32), ("advect_only", C.c_int32),
         ("device", C.c_int32), ("tile_begin", C.c_int32), ("tile_count", C.c_int32), ("kernel", C.c_int32),
-        ("fused_halo", C.c_int32), ("reserved", C.c_int32 * 3),
+        ("fused_halo", C.c_int32), ("sums_of_entry_state", C.c_int32), ("reserved", C.c_int32 * 2),
         ("radius", C.c_double), ("omega", C.c_double), ("gravity", C.c_double), ("axis", C.c_double * 3),
         ("tangents", C.POINTER(C.c_double)),
     ]
@@ -47,6 +48,7 @@ _PROTOTYPES = {
     "cs_set_topography": (C.c_int, [_VP, _VP, _VP]),
     "cs_rk_stage": (C.c_int, [_VP, _VP * 3, _VP * 3, _VP * 3, C.c_double, C.c_double, C.c_double, _VP, _VP]),
     "cs_rk_stage_part": (C.c_int, [_VP, _VP * 3, _VP * 3, _VP * 3, C.c_double, C.c_double, C.c_double, C.c_int, _VP]),
+    "cs_rk_stage_part_sums": (C.c_int, [_VP, _VP * 3, _VP * 3, _VP * 3, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, _VP, _VP]),
     "cs_step": (C.c_int, [_VP, _VP, _VP, _VP, C.c_double, _VP, _VP]),
     "cs_diagnostics": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     "cs_step_host": (C.c_int, [_VP, _VP, _VP, _VP, C.c_double, C.c_int, C.POINTER(C.c_double), C.c_int]),
@@ -57,6 +59,7 @@ _PROTOTYPES = {
     "cs_halo_pack": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP, _VP]),
     "cs_halo_unpack": (C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_launch_count": (C.c_int64, [_VP]),
+    "cs_stage_kernel_info": (C.c_int, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "cs_diagnostics_noalloc": (C.c_int, [C.c_int] * 6 + [C.c_double, C.c_double, _VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
 }
 

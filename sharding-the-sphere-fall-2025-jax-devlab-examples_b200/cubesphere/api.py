@@ -95,21 +95,19 @@ def setup_sharding(config, verbose=False):
     num_devices = int(para.get("num_devices", 6))
     tiles_per_edge = int(para.get("tiles_per_edge", 1))
     if tiles_per_edge < 1:
-        raise ValueError(f"Error: tiles_per_edge = {tiles_per_edge} must be >= 1.")
+        raise ValueError(f"tiles_per_edge must be a positive integer, got {tiles_per_edge}")
     if num_devices < 1:
-        raise ValueError(f"Error: num_devices = {num_devices} must be >= 1.")
+        raise ValueError(f"num_devices must be a positive integer, got {num_devices}")
     n_tiles = topology.num_tiles(tiles_per_edge)
     if num_devices > n_tiles:
         raise ValueError(
-            f"Error: num_devices = {num_devices} exceeds num_tiles = {n_tiles}.\n"
-            f"Cannot have more devices than tiles.\n"
-            f"With tiles_per_edge = {tiles_per_edge}, max devices = {n_tiles}.")
+            f"{num_devices} devices requested for a sphere of {n_tiles} tiles (tiles_per_edge = {tiles_per_edge}): "
+            f"every device needs at least one tile, so at most {n_tiles} devices can be used")
     if n_tiles % num_devices != 0:
         valid = [d for d in range(1, n_tiles + 1) if n_tiles % d == 0]
         raise ValueError(
-            f"Error: num_tiles = {n_tiles} is not evenly divisible by num_devices = {num_devices}.\n"
-            f"Block sharding of the tile axis requires: num_tiles % num_devices == 0\n"
-            f"With tiles_per_edge = {tiles_per_edge}, valid device counts are:\n  {valid}")
+            f"{n_tiles} tiles (tiles_per_edge = {tiles_per_edge}) cannot be split evenly over {num_devices} devices; "
+            f"the tile axis is block-partitioned, so use one of {valid}")
     if device_type == "cpu":
         devices = tuple(("cpu", k) for k in range(num_devices))
     elif device_type == "gpu":
@@ -120,10 +118,10 @@ def setup_sharding(config, verbose=False):
         if torch.distributed.is_available() and torch.distributed.is_initialized():
             world = torch.distributed.get_world_size()
         if num_devices > max(avail, world):
-            raise ValueError(f"Error: num_devices = {num_devices} but only {max(avail, world)} CUDA device(s) are available.")
+            raise ValueError(f"{num_devices} devices requested, {max(avail, world)} CUDA device(s) visible")
         devices = tuple(("cuda", k) for k in range(num_devices))
     else:
-        raise ValueError(f"Unknown device_type: {device_type}")
+        raise ValueError(f"device_type must be 'gpu' or 'cpu', got {device_type!r}")
     mesh = TileMesh(devices)
     sharding = TileSharding(mesh, n_tiles)
     if verbose:
@@ -185,7 +183,7 @@ def validate_schedule(schedule):
         faces = []
         for (fa, ea), (fb, eb), ops in stage:
             if ops not in ("N", "T", "R", "TR"):
-                raise ValueError(f"Unknown operation: {ops}")
+                raise ValueError(f"seam operation must be one of N, T, R, TR; got {ops!r}")
             nb, ne, _, _ = topology.neighbour(fa, ea)
             if (nb, ne) != (fb, eb):
                 raise ValueError(f"({fa},{ea}) <-> ({fb},{eb}) is not a cube seam; ({fa},{ea}) meets ({nb},{ne})")
@@ -221,7 +219,7 @@ class Context:
 
     def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f64", rk="ssprk3", limiter="mc", advect_only=False,
                  device=0, tile_begin=0, tile_count=0, kernel="auto", fused_halo=False, radius=0.0, omega=0.0,
-                 gravity=0.0, axis=(0.0, 0.0, 1.0), tangents=None):
+                 gravity=0.0, axis=(0.0, 0.0, 1.0), tangents=None, sums_of_entry_state=False):
         self._lib = B.lib()
         self.dtype = _torch_dtype(dtype)
         if rk not in B.RK_IDS:
@@ -238,6 +236,7 @@ class Context:
         cfg.advect_only = int(bool(advect_only))
         cfg.device, cfg.tile_begin, cfg.tile_count = int(device), int(tile_begin), int(tile_count)
         cfg.kernel, cfg.fused_halo = B.KERNEL_IDS[kernel], int(bool(fused_halo))
+        cfg.sums_of_entry_state = int(bool(sums_of_entry_state))
         cfg.radius, cfg.omega, cfg.gravity = float(radius), float(omega), float(gravity)
         for k in range(3):
             cfg.axis[k] = float(axis[k])
@@ -296,6 +295,14 @@ class Context:
     def launches(self):
         return int(self._lib.cs_launch_count(self._h))
 
+    def stage_kernel_info(self):
+        """(variant name of the last stage launch, number of launches an 'auto' context had to send to the
+        one-thread-per-cell kernel because the layout was not vectorisable)."""
+        last, falls = C.c_int32(0), C.c_int64(0)
+        self._check(self._lib.cs_stage_kernel_info(self._h, C.byref(last), C.byref(falls)))
+        names = {v: k for k, v in B.KERNEL_IDS.items()}
+        return names.get(last.value, str(last.value)), int(falls.value)
+
     # -- halo -----------------------------------------------------------------
     def halo_fill_scalar(self, field):
         self._check(self._lib.cs_halo_fill_scalar(self._h, self._ptr(field), self._stream()))
@@ -341,15 +348,19 @@ class Context:
     def _triple(self, q, name):
         return (C.c_void_p * 3)(*[self._ptr(t, f"{name}[{k}]") for k, t in enumerate(q)])
 
-    def rk_stage(self, q0, qs, qout, a, b, dt, diag=None, part=None):
+    def rk_stage(self, q0, qs, qout, a, b, dt, diag=None, part=None, sums_of_input=False):
         q0p = self._triple(q0, "q0") if q0 is not None else (C.c_void_p * 3)(None, None, None)
         if part is None:
             dp = C.c_void_p(diag.data_ptr()) if diag is not None else None
             self._check(self._lib.cs_rk_stage(self._h, q0p, self._triple(qs, "qs"), self._triple(qout, "qout"),
                                               float(a), float(b), float(dt), dp, self._stream()))
         else:
-            self._check(self._lib.cs_rk_stage_part(self._h, q0p, self._triple(qs, "qs"), self._triple(qout, "qout"),
-                                                   float(a), float(b), float(dt), int(part), self._stream()))
+            # a split stage: ``diag`` receives the sums over the cells of this part only, of the new values or
+            # (sums_of_input) of qs at those cells
+            dp = C.c_void_p(diag.data_ptr()) if diag is not None else None
+            which = B.CS_SUMS_OF_INPUT if sums_of_input else B.CS_SUMS_OF_OUTPUT
+            self._check(self._lib.cs_rk_stage_part_sums(self._h, q0p, self._triple(qs, "qs"), self._triple(qout, "qout"),
+                                                        float(a), float(b), float(dt), int(part), which, dp, self._stream()))
         return qout
 
     def step(self, h, u, v, dt, diag=None):

@@ -180,3 +180,83 @@ def coriolis_coefficients(axis=(0.0, 0.0, 1.0)) -> np.ndarray:
     """
     axis = np.asarray(axis, dtype=np.float64)
     return np.array([[axis @ np.asarray(v, dtype=np.float64) for v in frame] for frame in FACE_FRAMES])
+
+
+# ----------------------------------------------------------------------------
+# vector halo: geometric seam rotation  (no counterpart in the reference, which exchanges
+# Cartesian components instead -- deck slide 18)
+# ----------------------------------------------------------------------------
+
+def chart_basis(face, P, a=EARTH_RADIUS):
+    """Tangent basis (d r / d alpha, d r / d beta) of ``face``'s gnomonic chart at unit points ``P [..., 3]``.
+
+    The chart of a face covers its whole hemisphere, so ``P`` may lie beyond the face's own edges (ghost cells):
+    X = (P . x_f) / (P . n_f), Y = (P . y_f) / (P . n_f).  ``face`` is an int or an int array broadcastable to
+    ``P.shape[:-1]``.  Returns ``(e_a, e_b, X, Y)``.
+    """
+    fr = np.asarray(FACE_FRAMES, dtype=np.float64)[np.asarray(face)]
+    nrm, ex, ey = fr[..., 0, :], fr[..., 1, :], fr[..., 2, :]
+    pn = np.sum(P * nrm, -1)
+    if np.any(pn <= 0):
+        raise ValueError("a point lies outside the hemisphere of the chart it is to be expressed in")
+    X = np.sum(P * ex, -1) / pn
+    Y = np.sum(P * ey, -1) / pn
+    rho = np.sqrt(1.0 + X * X + Y * Y)
+    Q = nrm + X[..., None] * ex + Y[..., None] * ey
+    e_a = a * (1.0 + X * X)[..., None] * (ex / rho[..., None] - Q * (X / rho ** 3)[..., None])
+    e_b = a * (1.0 + Y * Y)[..., None] * (ey / rho[..., None] - Q * (Y / rho ** 3)[..., None])
+    return e_a, e_b, X, Y
+
+
+def seam_rotation(dst_face, src_face, src_X, src_Y, kind="contravariant", a=EARTH_RADIUS):
+    """2 x 2 matrices that re-express a vector held in ``src_face``'s chart at the point (src_X, src_Y) of that chart
+    in the (extended) chart of ``dst_face``:   (u, v)_dst = R (u, v)_src.
+
+    With B = [d r/d alpha, d r/d beta] (3 x 2) of either chart at the same point P and G = B^T B:
+      contravariant components (what this solver carries):  R = G_dst^-1 B_dst^T B_src,
+      covariant components:                                 R = B_dst^T B_src G_src^-1.
+    Same face -> the exact identity.  All arguments broadcast; the result has shape ``[..., 2, 2]``.
+    """
+    if kind not in ("contravariant", "covariant"):
+        raise ValueError(f"kind must be 'contravariant' or 'covariant', got {kind!r}")
+    dst_face, src_face = np.asarray(dst_face), np.asarray(src_face)
+    src_X, src_Y = np.asarray(src_X, dtype=np.float64), np.asarray(src_Y, dtype=np.float64)
+    fr = np.asarray(FACE_FRAMES, dtype=np.float64)[src_face]
+    P = fr[..., 0, :] + src_X[..., None] * fr[..., 1, :] + src_Y[..., None] * fr[..., 2, :]
+    P = P / np.linalg.norm(P, axis=-1, keepdims=True)
+    sa, sb, _, _ = chart_basis(src_face, P, a)
+    da, db, _, _ = chart_basis(np.broadcast_to(dst_face, src_X.shape), P, a)
+    Bs = np.stack([sa, sb], -1)                           # [..., 3, 2]
+    Bd = np.stack([da, db], -1)
+    M = np.einsum("...ki,...kj->...ij", Bd, Bs)           # B_dst^T B_src
+    if kind == "contravariant":
+        G = np.einsum("...ki,...kj->...ij", Bd, Bd)
+        R = np.linalg.solve(G, M)
+    else:
+        G = np.einsum("...ki,...kj->...ij", Bs, Bs)
+        R = np.einsum("...ij,...jk->...ik", M, np.linalg.inv(G))
+    same = np.broadcast_to(dst_face == src_face, R.shape[:-2])
+    R = np.where(same[..., None, None], np.eye(2), R)
+    return R
+
+
+def seam_rotation_tables(N, g, p=1, kind="contravariant", a=EARTH_RADIUS, table=None):
+    """Rotation matrix of every ghost cell, ``[n_ghost, 2, 2]`` fp64, host-precomputed.
+
+    Ghost cell k of :func:`topology.build_halo_table` (or of ``table`` = a dict with the same keys, e.g. decoded from
+    a context's ``halo_table()``) holds a copy of the interior cell ``(src_tile, src_j, src_i)``; row k re-expresses
+    that cell's panel-local vector in the extended chart of the ghost's own face, at the source cell's centre.
+    Corner blocks resolve to the E / W ghost column they extrapolate, so they get that column's matrix
+    ("already-rotated components").  Pass the result to ``Context.set_rotation`` / ``cs_halo_set_rotation``.
+    """
+    from . import topology
+    tab = topology.build_halo_table(N, p, g) if table is None else table
+    n = N // p
+    t = centre_tangents(N)
+    pp = p * p
+    src_face = tab["src_tile"] // pp
+    dst_face = tab["dst_tile"] // pp
+    r = tab["src_tile"] % pp
+    sx = t[(r % p) * n + tab["src_i"] - g]
+    sy = t[(r // p) * n + tab["src_j"] - g]
+    return seam_rotation(dst_face, src_face, sx, sy, kind, a)

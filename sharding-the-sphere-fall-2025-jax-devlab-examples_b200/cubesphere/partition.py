@@ -22,11 +22,10 @@ from . import topology
 def block_ranges(num_tiles: int, world: int):
     """[(tile_begin, tile_count)] per rank; requires num_tiles % world == 0 (reference PY:50)."""
     if world < 1 or world > num_tiles:
-        raise ValueError(f"Error: num_devices = {world} exceeds num_tiles = {num_tiles}.")
+        raise ValueError(f"{world} devices requested for {num_tiles} tiles: every device needs at least one tile")
     if num_tiles % world:
         valid = [d for d in range(1, num_tiles + 1) if num_tiles % d == 0]
-        raise ValueError(f"Error: num_tiles = {num_tiles} is not evenly divisible by num_devices = {world}.\n"
-                         f"valid device counts are:\n  {valid}")
+        raise ValueError(f"{num_tiles} tiles cannot be split evenly over {world} devices; use one of {valid}")
     per = num_tiles // world
     return [(r * per, per) for r in range(world)]
 

@@ -33,7 +33,10 @@ RK_PAIRS = {
 class ShardedStepper:
     def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f32", rk="ssprk3", limiter="mc", advect_only=False,
                  axis=(0.0, 0.0, 1.0), device=0, rank=0, world=1, kernel="auto", tangents=None, overlap=True,
-                 group=None, use_graph=True):
+                 group=None, use_graph=True, sums_of_entry_state=False):
+        # sums_of_entry_state: step(..., diag) reports mass / energy of the state the step STARTS from, summed inside
+        # the first stage's launches (a few instructions per cell); default: of the new state, inside the last stage's
+        self.sums_of_entry_state = bool(sums_of_entry_state)
         self.rank, self.world, self.rk, self.overlap, self.group = rank, world, rk, overlap, group
         # world > 1: a step is ~30 host calls (kernel launches, stream waits, one NCCL all-to-all per stage);
         # captured once into a CUDA graph per (dt, state tensors) and replayed, so the host never paces the GPUs
@@ -44,10 +47,12 @@ class ShardedStepper:
         self.tile_begin, self.tile_count = self.ranges[rank]
         self.ctx = api.Context(N, tiles_per_edge=tiles_per_edge, halo=halo, dtype=dtype, rk=rk, limiter=limiter,
                                advect_only=advect_only, axis=axis, device=device, kernel=kernel, tangents=tangents,
+                               sums_of_entry_state=sums_of_entry_state,
                                tile_begin=self.tile_begin, tile_count=self.tile_count if world > 1 else 0)
         self.n, self.m, self.device = self.ctx.n, self.ctx.m, device
         self._scratch = None
         self._extra_launches = 0
+        self._skip_exchange = False      # measurement only (time_halo): a step with the cross-GPU exchange left out
         if world > 1:
             self.send_counts, self.recv_counts = self.ctx.halo_plan([b for b, _ in self.ranges],
                                                                     [c for _, c in self.ranges])
@@ -58,6 +63,8 @@ class ShardedStepper:
             self.qa = [self.ctx.new_field() for _ in range(3)]
             self.qb = [self.ctx.new_field() for _ in range(3)]
             self._diag = torch.zeros(2, dtype=torch.float64, device=dev)
+            self._sums4 = torch.zeros(4, dtype=torch.float64, device=dev)    # [inner mass, energy, rim mass, energy]
+        self.halo_path = "single device: one ghost-fill launch" if world == 1 else "pack -> NCCL all_to_all_single -> unpack"
 
     # -- bookkeeping ------------------------------------------------------------------------
     @property
@@ -73,6 +80,8 @@ class ShardedStepper:
     # -- halo -------------------------------------------------------------------------------
     def _exchange(self, h, u, v, nfields=3):
         """pack -> all-to-all -> unpack on the current stream (remote ghosts only)."""
+        if self._skip_exchange:
+            return
         self.ctx.halo_pack(h, u, v, self.sendbuf, nfields)
         ns = nfields * sum(self.send_counts)
         nr = nfields * sum(self.recv_counts)
@@ -97,25 +106,28 @@ class ShardedStepper:
         self.ctx.set_topography(hs)
 
     # -- step -------------------------------------------------------------------------------
-    def step(self, h, u, v, dt):
+    def step(self, h, u, v, dt, diag=None):
+        """One time step in place.  ``diag`` (device fp64 tensor [2], optional) receives mass and total energy of the
+        new state, whole sphere: the sums come out of the last stage's launches (no extra pass over the state), and
+        across ranks they are combined by one all-reduce of four doubles."""
         if self.world == 1:
-            self.ctx.step(h, u, v, dt)
+            self.ctx.step(h, u, v, dt, diag=diag)
             return h, u, v
         if not self.use_graph:
-            return self._step_sharded(h, u, v, dt)
-        key = (float(dt), h.data_ptr(), u.data_ptr(), v.data_ptr())
+            return self._step_sharded(h, u, v, dt, diag)
+        key = (float(dt), h.data_ptr(), u.data_ptr(), v.data_ptr(), diag.data_ptr() if diag is not None else 0)
         graph = self._graphs.get(key)
         if graph is None:
             # the first two calls run eagerly (NCCL warm-up, lazy initialisation), the third is captured
             n = self._eager_calls.get(key, 0)
             if n < 2:
                 self._eager_calls[key] = n + 1
-                return self._step_sharded(h, u, v, dt)
+                return self._step_sharded(h, u, v, dt, diag)
             torch.cuda.synchronize(self.device)
             graph = torch.cuda.CUDAGraph()
             launches0 = self.ctx.launches
             with torch.cuda.graph(graph):
-                self._step_sharded(h, u, v, dt)
+                self._step_sharded(h, u, v, dt, diag)
             self._graph_launches = self.ctx.launches - launches0     # kernels of ours inside one replay
             self._graphs[key] = graph
             self._extra_launches -= self._graph_launches              # counted once by the capture itself
@@ -124,7 +136,7 @@ class ShardedStepper:
         self._extra_launches += self._graph_launches
         return h, u, v
 
-    def _step_sharded(self, h, u, v, dt):
+    def _step_sharded(self, h, u, v, dt, diag=None):
         q0 = (h, u, v)
         cur = q0
         pairs = RK_PAIRS[self.rk]
@@ -133,6 +145,9 @@ class ShardedStepper:
         for k, (a, b) in enumerate(pairs):
             last = k == len(pairs) - 1 and len(pairs) > 1
             out = q0 if last else (self.qa if k % 2 == 0 else self.qb)
+            # the last stage also sums mass / energy of its output -- or the first one those of its input
+            sin = self.sums_of_entry_state
+            sums = diag is not None and k == (0 if sin else len(pairs) - 1)
             if self.overlap:
                 # side stream: rim cells -> same-rank ghosts -> pack -> all-to-all -> unpack;
                 # main stream: the inner cells, which is where the time goes.
@@ -144,24 +159,30 @@ class ShardedStepper:
                         self.comm_stream.wait_stream(main)                     # whatever came before the step
                     else:
                         self.comm_stream.wait_event(ev_inner)                  # rim reads inner cells next to it
-                    self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1)
+                    self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1, diag=self._sums4[2:] if sums else None, sums_of_input=sin)
                     ev_rim_new = torch.cuda.Event()
                     ev_rim_new.record(self.comm_stream)
                     self.ctx.halo_fill_state(*out)
                     self._exchange(*out)
                 if ev_rim is not None:
                     main.wait_event(ev_rim)                                    # inner reads the previous rim cells
-                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=0)
+                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=0, diag=self._sums4[:2] if sums else None, sums_of_input=sin)
                 ev_inner = torch.cuda.Event()
                 ev_inner.record(main)
                 ev_rim = ev_rim_new
             else:
-                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=2)
+                if sums:
+                    self._sums4[2:].zero_()
+                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=2, diag=self._sums4[:2] if sums else None, sums_of_input=sin)
                 self.ctx.halo_fill_state(*out)
                 self._exchange(*out)
             cur = out
         if self.overlap:
             main.wait_stream(self.comm_stream)
+        if diag is not None:
+            # rank-local (inner, rim) sums -> whole sphere: one all-reduce of four doubles, then inner + rim
+            dist.all_reduce(self._sums4, group=self.group)
+            torch.add(self._sums4[:2], self._sums4[2:], out=diag)
         if len(pairs) == 1:
             for x, y in zip(q0, cur):
                 x.copy_(y)
@@ -175,27 +196,95 @@ class ShardedStepper:
         return out
 
     # -- measurement helpers used by bench.py ---------------------------------------------------
-    def time_stage_kernel(self, state, dt, reps=5):
-        """CUDA-event time of each fused-stage launch alone (all owned cells, no halo)."""
+    def time_stage_kernel(self, state, dt, reps=10, rounds=3):
+        """Device time of each fused-stage launch alone (all owned cells, no halo): ``reps`` launches of one stage
+        are captured into a CUDA graph and the replay is timed with CUDA events, so host launch gaps are not in the
+        number (an eager loop under-reports the kernel, most of all for the short fp32 launches); best of
+        ``rounds`` replays.  The last stage is the variant a step with diagnostics runs (sums fused in)."""
         if self._scratch is None:
             self._scratch = [self.ctx.new_field() for _ in range(3)]
             self._q0 = [x.clone() for x in state]      # distinct from qs, as in stages 2 and 3 of a real step
+            self._stage_diag = torch.zeros(2, dtype=torch.float64, device=f"cuda:{self.device}")
         pairs = RK_PAIRS[self.rk]
-        ms = [0.0] * len(pairs)
+        ms, sums_us = [0.0] * len(pairs), None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+        def timed(launch):
+            launch()                                                              # warm (lazy module load)
+            torch.cuda.synchronize(self.device)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                for _ in range(reps):
+                    launch()
+            graph.replay()
+            torch.cuda.synchronize(self.device)
+            best = float("inf")
+            for _ in range(rounds):
+                e0.record()
+                graph.replay()
+                e1.record()
+                torch.cuda.synchronize(self.device)
+                best = min(best, e0.elapsed_time(e1) / reps)
+            del graph
+            return best
+
         for k, (a, b) in enumerate(pairs):
-            self.ctx.rk_stage(self._q0, state, self._scratch, a, b, dt, part=2)   # warm
-            torch.cuda.synchronize()
+            ms[k] = timed(lambda: self.ctx.rk_stage(self._q0, state, self._scratch, a, b, dt, part=2))
+        if self.world == 1:
+            # what the fused conservation sums add to a stage launch: of the output (last stage of a step that wants the
+            # new state's sums) and of the input (first stage, sums of the entry state)
+            a, b = pairs[-1]
+            d = self._stage_diag
+            out_us = (timed(lambda: self.ctx.rk_stage(self._q0, state, self._scratch, a, b, dt, part=2, diag=d)) - ms[-1]) * 1e3
+            a, b = pairs[0]
+            in_us = (timed(lambda: self.ctx.rk_stage(self._q0, state, self._scratch, a, b, dt, part=2, diag=d, sums_of_input=True))
+                     - ms[0]) * 1e3
+            sums_us = {"of_new_state_in_last_stage": out_us, "of_entry_state_in_first_stage": in_us}
+        return {"a": [a for a, _ in pairs], "ms": ms, "fused_sums_us": sums_us,
+                "kernel": "stage_march_kernel (fused RK stage)", "how": f"{reps} launches per CUDA graph, best of {rounds} replays"}
+
+    def time_halo(self, state, dt, reps=20):
+        """Cross-GPU halo numbers (world > 1): ``exchange_us`` = pack + all-to-all + unpack alone, per fill;
+        ``step_ms_without_exchange`` = the step with the exchange left out (wrong ghosts, same kernels), from which
+        the caller gets the exposed halo time per step."""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(3):
+            self._exchange(*state)
+        dist.barrier(group=self.group)
+        torch.cuda.synchronize(self.device)
+        e0.record()
+        for _ in range(reps):
+            self._exchange(*state)
+        e1.record()
+        torch.cuda.synchronize(self.device)
+        exch_us = e0.elapsed_time(e1) * 1e3 / reps
+        # the same step without the exchange: scratch state (the result is not physical), eager launches are replaced
+        # by a graph exactly as in step()
+        scratch = [x.clone() for x in state]
+        self._skip_exchange = True
+        saved = (self._graphs, self._eager_calls)
+        self._graphs, self._eager_calls = {}, {}
+        try:
+            for _ in range(4):
+                self.step(*scratch, dt)
+            dist.barrier(group=self.group)
+            torch.cuda.synchronize(self.device)
             e0.record()
             for _ in range(reps):
-                self.ctx.rk_stage(self._q0, state, self._scratch, a, b, dt, part=2)
+                self.step(*scratch, dt)
             e1.record()
-            torch.cuda.synchronize()
-            ms[k] = e0.elapsed_time(e1) / reps
-        return {"a": [a for a, _ in pairs], "ms": ms, "kernel": "cs stage kernel (fused RK stage)"}
+            torch.cuda.synchronize(self.device)
+        finally:
+            self._skip_exchange = False
+            self._graphs, self._eager_calls = saved
+        t = torch.tensor([exch_us, e0.elapsed_time(e1) / reps], device=f"cuda:{self.device}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return {"exchange_us": float(t[0].item()), "step_ms_without_exchange": float(t[1].item())}
 
     def time_e2e(self, pinned, dev, dt, nsteps, cells_total):
-        """Sharded end-to-end: per step H2D of the shard from pinned memory, the step, D2H of [mass, energy]."""
+        """Sharded end-to-end round trip: per step H2D of the shard from pinned memory, halo fill, the step, D2H of
+        the new state into pinned memory and of [mass, energy]."""
+        back = [torch.empty_like(p).pin_memory() for p in pinned]
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         for warm in (True, False):
             if not warm:
@@ -207,6 +296,8 @@ class ShardedStepper:
                     d.copy_(p, non_blocking=True)
                 self.halo_fill(*dev)
                 self.step(*dev, dt)
+                for b, d in zip(back, dev):
+                    b.copy_(d, non_blocking=True)
                 self.diagnostics(*dev).cpu()
         e1.record()
         torch.cuda.synchronize()
@@ -214,4 +305,6 @@ class ShardedStepper:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         nbytes = sum(x.numel() * x.element_size() for x in pinned)
         return {"value": cells_total / (float(t.item()) * 1e-3), "unit": "cell-updates/s",
-                "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 16, "ms_per_step": float(t.item())}
+                "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes + 16, "ms_per_step": float(t.item()),
+                "call": "per rank: H2D of its shard (pinned), halo fill + exchange, step, D2H of the shard and of "
+                        "[mass, energy]; bytes are per rank"}

@@ -131,7 +131,7 @@ def create_tile_schedule(tiles_per_edge: int = 1):
     """
     p = int(tiles_per_edge)
     if p < 1:
-        raise ValueError(f"Error: tiles_per_edge = {p} must be >= 1.")
+        raise ValueError(f"tiles_per_edge must be a positive integer, got {p}")
     if p == 1:
         return create_communication_schedule()
     desc = edge_push_descriptors(p)
@@ -207,7 +207,7 @@ def apply_operations(data, operations: str):
         return data
     if operations in ("R", "TR"):
         return data.flip(-1) if hasattr(data, "flip") else data[..., ::-1]
-    raise ValueError(f"Unknown operation: {operations}")
+    raise ValueError(f"seam operation must be one of N, T, R, TR; got {operations!r}")
 
 
 def perm_code(S: np.ndarray) -> int:

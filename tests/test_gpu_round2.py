@@ -1,0 +1,281 @@
+"""Round-2 GPU tests: fused conservation sums, tiny tiles in the split stage, kernel bookkeeping, device hygiene.
+
+All through the C ABI (ctypes), all against the CPU oracle or against another product path that is itself held to the
+oracle elsewhere in this suite.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+pytestmark = pytest.mark.gpu
+
+from cubesphere import api, cases  # noqa: E402
+from oracle import cs_oracle_np as orc  # noqa: E402
+
+
+def _setup(name, N, p, dtype, g=2, **ctx_kw):
+    case = cases.make_case(name, N)
+    par = orc.Params(N, g, axis=case.axis, advect_only=case.advect_only, hs=case.hs)
+    ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
+    ctx = api.Context(N, tiles_per_edge=p, halo=g, dtype=dtype, advect_only=case.advect_only, axis=case.axis,
+                      tangents=orc.centre_tangents(N), **ctx_kw)
+    dev = [torch.from_numpy(orc.faces_to_tiles(x, p, g).astype(dtype)).cuda() for x in ref]
+    if case.hs is not None:
+        ctx.set_topography(torch.from_numpy(orc.faces_to_tiles(par.hs, p, g).astype(dtype)).cuda())
+    return case, par, ref, ctx, dev
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# K3 fused into the last stage of a step
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("name,N,p", [("tc5", 96, 1), ("tc2", 48, 2), ("galewsky", 64, 1)])
+def test_fused_step_diagnostics_fp64(built_library, name, N, p):
+    """cs_step(..., diag_out): the sums come out of the last stage kernel.  fp64: mass 1e-13 / energy 1e-12 against
+    the oracle and against the stand-alone reduction kernel on the same state; identical bits run to run."""
+    case, par, ref, ctx, dev = _setup(name, N, p, np.float64)
+    dt = cases.stable_dt(case, 0.5)
+    diag = torch.full((2,), float("nan"), dtype=torch.float64, device="cuda")
+    start = [x.clone() for x in dev]
+    for _ in range(3):
+        ctx.step(*dev, dt, diag=diag)
+        ref = orc.step(par, ref, dt)
+    assert ctx.stage_kernel_info()[0] == "march"
+    got = diag.cpu().numpy()
+    sep = ctx.diagnostics(*dev).cpu().numpy()
+    want = np.array(orc.diagnostics(par, *ref))
+    for other in (sep, want):
+        assert abs(got[0] - other[0]) <= 1e-13 * abs(other[0]), (got, other)
+        assert abs(got[1] - other[1]) <= 1e-12 * abs(other[1]), (got, other)
+    # the same three steps again from the same start: the same bits (fixed summation order, no atomics on the sums)
+    again = torch.zeros(2, dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        ctx.step(*start, dt, diag=again)
+    assert torch.equal(again, diag) and all(torch.equal(a, b) for a, b in zip(start, dev))
+    ctx.close()
+
+
+@pytest.mark.parametrize("entry", [False, True])
+def test_fused_step_diagnostics_fp32(built_library, entry):
+    """fp32 state: per-cell products are formed in fp32 (with the kernel's own fp32 metric) and accumulated in fp64.
+    Against the all-fp64 reduction kernel on the same fp32 state the sums carry a constant relative offset of a few
+    1e-8 (MUFU.RSQ in sqrt(G) is biased by a fraction of an ulp, and sqrt(G) ~ rsqrt^3): stated tolerance 1e-7.  The
+    offset is a property of the grid, not of the state, so CHANGES of mass are seen much more finely: 2e-9."""
+    case, par, ref, ctx, dev = _setup("tc5", 192, 1, np.float32, sums_of_entry_state=entry)
+    dt = cases.stable_dt(case, 0.5)
+    diag = torch.zeros(2, dtype=torch.float64, device="cuda")
+    fused, sep = [], []
+    for _ in range(4):
+        if entry:
+            sep.append(ctx.diagnostics(*dev).cpu().numpy())      # the state the step starts from
+        ctx.step(*dev, dt, diag=diag)
+        if not entry:
+            sep.append(ctx.diagnostics(*dev).cpu().numpy())      # the new state
+        fused.append(diag.cpu().numpy().copy())
+    fused, sep = np.array(fused), np.array(sep)
+    rel = np.abs(fused - sep) / np.abs(sep)
+    print(f"fp32 fused (entry={entry}) vs fp64 reduction: mass {rel[:, 0].max():.2e}, energy {rel[:, 1].max():.2e}")
+    assert rel.max() <= 1e-7, (fused, sep)
+    drift_f = (fused[-1, 0] - fused[0, 0]) / fused[0, 0]
+    drift_s = (sep[-1, 0] - sep[0, 0]) / sep[0, 0]
+    assert abs(drift_f - drift_s) <= 2e-9, (drift_f, drift_s)
+    ctx.close()
+
+
+@pytest.mark.parametrize("name,N,p", [("tc5", 96, 1), ("tc2", 48, 2)])
+def test_entry_state_sums_fp64(built_library, name, N, p):
+    """sums_of_entry_state = 1: cs_step's diag_out is mass / energy of the state the step starts from, summed inside
+    the FIRST stage launch.  fp64: 1e-13 / 1e-12 against the oracle's diagnostics of that state; same bits on a rerun."""
+    case, par, ref, ctx, dev = _setup(name, N, p, np.float64, sums_of_entry_state=True)
+    dt = cases.stable_dt(case, 0.5)
+    diag = torch.full((2,), float("nan"), dtype=torch.float64, device="cuda")
+    start = [x.clone() for x in dev]
+    for _ in range(3):
+        want = np.array(orc.diagnostics(par, *ref))
+        ctx.step(*dev, dt, diag=diag)
+        got = diag.cpu().numpy()
+        assert abs(got[0] - want[0]) <= 1e-13 * abs(want[0]), (got, want)
+        assert abs(got[1] - want[1]) <= 1e-12 * abs(want[1]), (got, want)
+        ref = orc.step(par, ref, dt)
+    again = torch.zeros(2, dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        ctx.step(*start, dt, diag=again)
+    assert torch.equal(again, diag) and all(torch.equal(a, b) for a, b in zip(start, dev))
+    ctx.close()
+
+
+def test_fused_diag_can_be_switched_off_and_stage_entry_agrees(built_library):
+    """CS_FUSED_DIAG=0 (read when the context is created) sends diag_out through the reduction kernel; cs_rk_stage
+    with diag_out gives the fused numbers too."""
+    os.environ["CS_FUSED_DIAG"] = "0"
+    try:
+        case, par, ref, ctx0, dev0 = _setup("tc5", 48, 1, np.float64)
+    finally:
+        del os.environ["CS_FUSED_DIAG"]
+    _, _, _, ctx1, dev1 = _setup("tc5", 48, 1, np.float64)
+    dt = cases.stable_dt(case, 0.5)
+    d0 = torch.zeros(2, dtype=torch.float64, device="cuda")
+    d1 = torch.zeros(2, dtype=torch.float64, device="cuda")
+    ctx0.step(*dev0, dt, diag=d0)
+    ctx1.step(*dev1, dt, diag=d1)
+    assert all(torch.equal(a, b) for a, b in zip(dev0, dev1))        # the state does not depend on who sums
+    a, b = d0.cpu().numpy(), d1.cpu().numpy()
+    assert abs(a[0] - b[0]) <= 1e-13 * abs(a[0]) and abs(a[1] - b[1]) <= 1e-12 * abs(a[1])
+    # one stage through cs_rk_stage
+    out = [ctx1.new_field() for _ in range(3)]
+    ds = torch.zeros(2, dtype=torch.float64, device="cuda")
+    ctx1.rk_stage(dev1, dev1, out, 0.75, 0.25, dt, diag=ds)
+    sep = ctx1.diagnostics(*out).cpu().numpy()
+    got = ds.cpu().numpy()
+    assert abs(got[0] - sep[0]) <= 1e-13 * abs(sep[0]) and abs(got[1] - sep[1]) <= 1e-12 * abs(sep[1])
+    ctx0.close(), ctx1.close()
+
+
+@pytest.mark.parametrize("of_input", [False, True])
+@pytest.mark.parametrize("dtype,N,p", [(np.float64, 48, 2), (np.float64, 96, 1), (np.float32, 96, 2)])
+def test_split_stage_sums_add_up(built_library, dtype, N, p, of_input):
+    """cs_rk_stage_part_sums: inner-part sums (marching kernel) + rim-part sums (rim kernel) = the sums of the whole
+    stage output (or input), which the stand-alone reduction kernel confirms."""
+    case, par, ref, ctx, dev = _setup("tc5", N, p, dtype)
+    dt = cases.stable_dt(case, 0.5)
+    out = [ctx.new_field() for _ in range(3)]
+    s4 = torch.full((4,), float("nan"), dtype=torch.float64, device="cuda")
+    ctx.rk_stage(dev, dev, out, 0.75, 0.25, dt, part=0, diag=s4[:2], sums_of_input=of_input)
+    ctx.rk_stage(dev, dev, out, 0.75, 0.25, dt, part=1, diag=s4[2:], sums_of_input=of_input)
+    got = (s4[:2] + s4[2:]).cpu().numpy()
+    want = ctx.diagnostics(*(dev if of_input else out)).cpu().numpy()
+    tol = (1e-13, 1e-12) if dtype is np.float64 else (1e-7, 1e-7)
+    assert abs(got[0] - want[0]) <= tol[0] * abs(want[0]) and abs(got[1] - want[1]) <= tol[1] * abs(want[1]), (got, want)
+    rim_share = float(s4[2] / (s4[0] + s4[2]))
+    n = N // p
+    assert abs(rim_share - (1 - (n - 4) ** 2 / n ** 2)) < 0.05          # the rim is the rim: about 8 / n of the cells
+    ctx.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# split stage on tiles with fewer than 2g cells per edge (every cell is a rim cell)
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("N,p", [(12, 4), (8, 4), (12, 3)])          # n = 3, 2, 4 with g = 2
+def test_split_stage_on_tiny_tiles(built_library, N, p):
+    case, par, ref, ctx, dev = _setup("tc2", N, p, np.float64)
+    dt = cases.stable_dt(case, 0.3)
+    whole = [torch.full_like(x, float("nan")) for x in dev]
+    split = [torch.full_like(x, float("nan")) for x in dev]
+    ctx.rk_stage(dev, dev, whole, 0.75, 0.25, dt, part=2)
+    ctx.rk_stage(dev, dev, split, 0.75, 0.25, dt, part=0)
+    ctx.rk_stage(dev, dev, split, 0.75, 0.25, dt, part=1)
+    g, n = 2, N // p
+    c = slice(g, g + n)
+    for a, b in zip(whole, split):
+        assert not torch.isnan(b[:, c, c]).any(), "a cell was written by neither part"
+        assert torch.equal(a[:, c, c], b[:, c, c])
+    # and the whole stage is the oracle's
+    want = orc.rk_stage(par, ref, ref, 0.75, 0.25, dt)
+    got = orc.tiles_to_faces(whole[0].cpu().numpy(), p, g)
+    cc = slice(g, g + N)
+    assert np.allclose(got[:, cc, cc], want[0][:, cc, cc], rtol=1e-13, atol=0)
+    ctx.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# bookkeeping and hygiene
+# ---------------------------------------------------------------------------------------------------------------
+
+def test_auto_fallback_to_the_slow_kernel_is_visible(built_library):
+    """An odd row length cannot be vectorised: 'auto' takes the one-thread-per-cell kernel, and says so."""
+    case, par, ref, ctx, dev = _setup("tc2", 25, 1, np.float64)     # m = 29
+    assert ctx.stage_kernel_info() == ("auto", 0)
+    dt = cases.stable_dt(case, 0.5)
+    ctx.step(*dev, dt)
+    name, falls = ctx.stage_kernel_info()
+    assert name == "naive" and falls == 3
+    ref = orc.step(par, ref, dt)
+    c = slice(2, 27)
+    assert np.allclose(dev[0].cpu().numpy()[:, c, c], ref[0][:, c, c], rtol=1e-13, atol=0)
+    ctx.close()
+    case, par, ref, ctx, dev = _setup("tc2", 24, 1, np.float64)
+    ctx.step(*dev, cases.stable_dt(case, 0.5))
+    assert ctx.stage_kernel_info() == ("march", 0)
+    ctx.close()
+
+
+def test_entry_points_restore_the_callers_device(built_library):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible GPUs")
+    rt = torch.cuda.cudart()
+    rt.cudaSetDevice(1)
+    try:
+        case, par, ref, ctx, dev = _setup("tc2", 24, 1, np.float64)   # context and state on cuda:0
+        assert torch.cuda.current_device() == 1
+        null = C.c_void_p(None)
+        lib = built_library
+        rc = lib.cs_halo_fill_state(ctx._h, *(C.c_void_p(x.data_ptr()) for x in dev), null)
+        assert rc == 0 and torch.cuda.current_device() == 1
+        rc = lib.cs_step(ctx._h, *(C.c_void_p(x.data_ptr()) for x in dev), cases.stable_dt(case, 0.5), null, null)
+        assert rc == 0 and torch.cuda.current_device() == 1
+        ctx.close()
+        assert torch.cuda.current_device() == 1
+    finally:
+        rt.cudaSetDevice(0)
+    torch.cuda.synchronize(0)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# a9: the vector halo with the geometric seam-rotation tables
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("N,p", [(24, 1), (16, 2)])
+def test_halo_with_geometric_rotation_tables(built_library, N, p):
+    """geometry.seam_rotation_tables installed with cs_halo_set_rotation: the rotated ghosts of a solid-body wind are
+    (1) bit-identical to the same two products and one sum in NumPy, and (2) the analytic wind's components in the
+    ghost's own extended chart at the neighbour's cell centre, to 1e-12."""
+    from cubesphere import geometry as geo
+    g = 2
+    n, m = N // p, N // p + 2 * g
+    ctx = api.Context(N, tiles_per_edge=p, halo=g, dtype=np.float64)
+    dst, src, code = ctx.halo_table()
+    tab = {"dst_tile": dst // (m * m), "dst_j": (dst % (m * m)) // m, "dst_i": dst % m,
+           "src_tile": src // (m * m), "src_j": (src % (m * m)) // m, "src_i": src % m, "code": code}
+    R = geo.seam_rotation_tables(N, g, p, "contravariant", table=tab)
+    ctx.set_rotation(R)
+    # solid-body wind about a tilted axis, contravariant components on every tile's interior
+    patch = geo.Patch(N, p)
+    P = patch.points()
+    w = np.array([0.3, -0.5, 0.8]) * 1e-5
+    V = geo.EARTH_RADIUS * np.cross(np.broadcast_to(w, P.shape), P)
+    u1, u2 = geo.contravariant_from_cartesian(V, N, patch=patch)
+    u = np.full((6 * p * p, m, m), np.nan)
+    v = np.full((6 * p * p, m, m), np.nan)
+    u[:, g:g + n, g:g + n], v[:, g:g + n, g:g + n] = u1, u2
+    du, dv = torch.from_numpy(u).cuda(), torch.from_numpy(v).cuda()
+    ctx.halo_fill_vector(du, dv)
+    gu, gv = du.cpu().numpy().reshape(-1), dv.cpu().numpy().reshape(-1)
+    a, b = u.reshape(-1)[src], v.reshape(-1)[src]
+    want_u = R[:, 0, 0] * a + R[:, 0, 1] * b              # NumPy: two products, one sum, no FMA
+    want_v = R[:, 1, 0] * a + R[:, 1, 1] * b
+    assert np.array_equal(gu[dst], want_u) and np.array_equal(gv[dst], want_v)
+    assert not np.isnan(gu).any() and not np.isnan(gv).any()        # every ghost cell was written
+    # analytic: the wind at the source cell's centre, expressed in the destination face's extended chart
+    t = geo.centre_tangents(N)
+    pp = p * p
+    sf, df = tab["src_tile"] // pp, tab["dst_tile"] // pp
+    r = tab["src_tile"] % pp
+    X, Y = t[(r % p) * n + tab["src_i"] - g], t[(r // p) * n + tab["src_j"] - g]
+    fr = np.asarray(geo.FACE_FRAMES, dtype=np.float64)[sf]
+    Ps = fr[:, 0] + X[:, None] * fr[:, 1] + Y[:, None] * fr[:, 2]
+    Ps /= np.linalg.norm(Ps, axis=-1, keepdims=True)
+    Vs = geo.EARTH_RADIUS * np.cross(np.broadcast_to(w, Ps.shape), Ps)
+    ea, eb, _, _ = geo.chart_basis(df, Ps)
+    g11, g12, g22 = np.sum(ea * ea, -1), np.sum(ea * eb, -1), np.sum(eb * eb, -1)
+    b1, b2 = np.sum(ea * Vs, -1), np.sum(eb * Vs, -1)
+    det = g11 * g22 - g12 * g12
+    au, av = (g22 * b1 - g12 * b2) / det, (g11 * b2 - g12 * b1) / det
+    scale = max(np.abs(au).max(), np.abs(av).max())
+    assert np.abs(gu[dst] - au).max() <= 1e-12 * scale and np.abs(gv[dst] - av).max() <= 1e-12 * scale
+    ctx.set_rotation(None)
+    ctx.close()

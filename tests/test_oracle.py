@@ -160,3 +160,31 @@ def test_c_halo_equals_numpy_halo():
     occ.halo_fill(N, g, h, u, v)
     for a, b in zip((h, u, v), ref):
         assert np.array_equal(a, b)
+
+
+def test_fp32_c_oracle_tracks_the_fp64_one():
+    """The single-precision build of the C oracle (bench.py's CPU arm in the GPU arm's precision) is the same scheme:
+    after 10 steps it differs from the fp64 oracle by fp32 round-off only, and its halo fill is bit-exact in fp32."""
+    N, g = 32, 2
+    case = cases.make_case("tc5", N)
+    p = _params(case)
+    st = [np.ascontiguousarray(x) for x in _state(case)]
+    c64 = occ.COracle(N, g, axis=case.axis, hs=p.hs)
+    c32 = occ.COracle(N, g, axis=case.axis, hs=p.hs.astype(np.float32), dtype=np.float32)
+    s64 = [x.copy() for x in st]
+    s32 = [x.astype(np.float32) for x in st]
+    m0, _ = c32.diagnostics(*s32)
+    dt = cases.stable_dt(case, 0.5)
+    c64.step(*s64, dt, 10)
+    c32.step(*s32, dt, 10)
+    c = slice(g, g + N)
+    err = np.linalg.norm(s32[0][:, c, c] - s64[0][:, c, c]) / np.linalg.norm(s64[0][:, c, c])
+    assert err < 2e-6, err
+    m1, _ = c32.diagnostics(*s32)
+    assert abs(m1 - m0) / m0 < 1e-6
+    rng = np.random.default_rng(7)
+    h, u, v = (rng.standard_normal((6, N + 2 * g, N + 2 * g)).astype(np.float32) for _ in range(3))
+    ref = orc.halo_fill_state(h, u, v, g)
+    occ.halo_fill(N, g, h, u, v)
+    for a, b in zip((h, u, v), ref):
+        assert a.dtype == np.float32 and np.array_equal(a, b)

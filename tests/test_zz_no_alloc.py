@@ -5,7 +5,8 @@ It exists for callers that cannot create a cs_ctx because they cannot allocate d
 hook on a latency-critical thread).  Its only scratch is a fixed static array inside the library,
 shared by every call on the device, so the checks below run it twice in a row on different data:
 the second call must not be disturbed by what the first one left in the array.  Results are
-compared with the context-based cs_diagnostics within the tolerances used elsewhere in this suite
+compared with the context-based cs_diagnostics AND, independently of any product kernel, with the
+NumPy oracle's diagnostics of the same numbers, within the tolerances used elsewhere in this suite
 (mass 1e-13, energy 1e-12, relative).  The file name sorts last on purpose.
 """
 import ctypes as C
@@ -41,6 +42,15 @@ def _state(name, N, p, g, dtype):
     return case, dev, hs
 
 
+def _oracle_diag(case, N, g, dtype):
+    """[mass, energy] by the NumPy oracle of exactly the numbers the device holds (rounded to fp32 when it is)."""
+    nd = np.float64 if dtype is torch.float64 else np.float32
+    rnd = lambda x: x.astype(nd).astype(np.float64)
+    par = orc.Params(N, g, axis=case.axis, hs=None if case.hs is None else rnd(case.hs))
+    faces = [rnd(x) for x in orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)]
+    return np.array(orc.diagnostics(par, *faces))
+
+
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
 def test_two_calls_in_a_row_match_context_diagnostics(built_library, dtype):
     lib = built_library
@@ -57,6 +67,9 @@ def test_two_calls_in_a_row_match_context_diagnostics(built_library, dtype):
         got = out.cpu().numpy()
         assert abs(got[0] - want[0]) <= 1e-13 * abs(want[0]), (name, got, want)
         assert abs(got[1] - want[1]) <= 1e-12 * abs(want[1]), (name, got, want)
+        ref = _oracle_diag(case, N, g, dtype)             # the independent CPU statement, no product code involved
+        assert abs(got[0] - ref[0]) <= 1e-13 * abs(ref[0]), (name, got, ref)
+        assert abs(got[1] - ref[1]) <= 1e-12 * abs(ref[1]), (name, got, ref)
         # same call again: bit-identical (fixed summation order, stale scratch ignored)
         rc, again = _noalloc(lib, dtype, N, p, g, *dev, hs=hs)
         assert rc == B.CS_OK and torch.equal(again, out)
@@ -82,3 +95,28 @@ def test_shard_range_and_limits(built_library):
     assert rc == B.CS_E_INVALID and b"exceed the fixed scratch" in lib.cs_last_error(None)
     rc, _ = _noalloc(lib, torch.float64, 50, 4, g, *dev)
     assert rc == B.CS_E_INVALID
+
+
+def test_callers_current_device_is_left_alone(built_library):
+    """The callers this entry point is for sit inside another framework's handler thread: the device that thread
+    had selected must still be selected when the call returns."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible GPUs to tell a restored device from an untouched one")
+    lib = built_library
+    g, N = 2, 24
+    case, dev, _ = _state("tc2", N, 1, g, torch.float64)          # state on cuda:0
+    rt = torch.cuda.cudart()
+    torch.cuda.synchronize(0)
+    rt.cudaSetDevice(1)
+    try:
+        out = torch.zeros(2, dtype=torch.float64, device="cuda:0")
+        rc = lib.cs_diagnostics_noalloc(B.CS_F64, N, 1, g, 0, 0, 0.0, 0.0, C.c_void_p(dev[0].data_ptr()),
+                                        C.c_void_p(dev[1].data_ptr()), C.c_void_p(dev[2].data_ptr()), None,
+                                        C.c_void_p(out.data_ptr()), 0, None)
+        assert rc == B.CS_OK
+        assert torch.cuda.current_device() == 1
+    finally:
+        rt.cudaSetDevice(0)
+    torch.cuda.synchronize(0)
+    ref = _oracle_diag(case, N, g, torch.float64)
+    assert np.all(np.abs(out.cpu().numpy() - ref) <= 1e-12 * np.abs(ref))

@@ -18,7 +18,7 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ok = True
-for N, p, overlap in ((48, 2 if world > 3 else 1, True), (96, 2, True), (96, 2, False)):
+for N, p, overlap, entry in ((48, 2 if world > 3 else 1, True, False), (96, 2, True, True), (96, 2, False, False)):
     if (6 * p * p) % world:
         continue
     g, steps = 2, 10
@@ -26,7 +26,7 @@ for N, p, overlap in ((48, 2 if world > 3 else 1, True), (96, 2, True), (96, 2, 
     par = orc.Params(N, g, axis=case.axis, hs=case.hs)
     ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
     st = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis, device=local, rank=rank,
-                                world=world, tangents=orc.centre_tangents(N), overlap=overlap)
+                                world=world, tangents=orc.centre_tangents(N), overlap=overlap, sums_of_entry_state=entry)
     b, c = st.tile_begin, st.tile_count
     n = N // p
     raw = [orc.faces_to_tiles(orc.pad(x, g), p, g)[b:b + c] for x in (case.h, case.u1, case.u2)]   # ghosts empty
@@ -36,10 +36,13 @@ for N, p, overlap in ((48, 2 if world > 3 else 1, True), (96, 2, True), (96, 2, 
     st.halo_fill(*dev)
     dt = cases.stable_dt(case)
     m0 = st.diagnostics(*dev).cpu().numpy()
+    fused = torch.zeros(2, dtype=torch.float64, device="cuda")
     for _ in range(steps):
-        st.step(*dev, dt)
+        mo_entry = orc.diagnostics(par, *ref)
+        st.step(*dev, dt, diag=fused)                  # sums fused into a stage's launches + one all-reduce
         ref = orc.step(par, ref, dt)
     m1 = st.diagnostics(*dev).cpu().numpy()
+    mf = fused.cpu().numpy()
     want = [orc.faces_to_tiles(x, p, g)[b:b + c] for x in ref]
     errs = []
     for got, w in zip(dev, want):
@@ -47,9 +50,11 @@ for N, p, overlap in ((48, 2 if world > 3 else 1, True), (96, 2, True), (96, 2, 
         errs.append(float(np.linalg.norm(a[:, g:g + n, g:g + n] - w[:, g:g + n, g:g + n]) / np.linalg.norm(w[:, g:g + n, g:g + n])))
         errs.append(float(np.linalg.norm(a[:, g:g + n, :] - w[:, g:g + n, :]) / np.linalg.norm(w[:, g:g + n, :])))
     mo = orc.diagnostics(par, *ref)
+    mfo = mo_entry if entry else mo                    # entry mode: the fused sums are those of the state before the last step
     good = max(errs) <= 1e-12 and abs(m1[0] - m0[0]) <= 1e-13 * m0[0] and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
+    good = good and abs(mf[0] - mfo[0]) <= 1e-13 * mfo[0] and abs(mf[1] - mfo[1]) <= 1e-12 * abs(mfo[1])
     ok = ok and good
-    print(f"rank {rank}/{world} C{N} p={p} overlap={overlap}: max rel err {max(errs):.2e}, mass drift {(m1[0]-m0[0])/m0[0]:.1e} -> {'ok' if good else 'FAIL'}", flush=True)
+    print(f"rank {rank}/{world} C{N} p={p} overlap={overlap} entry_sums={entry}: max rel err {max(errs):.2e}, mass drift {(m1[0]-m0[0])/m0[0]:.1e} -> {'ok' if good else 'FAIL'}", flush=True)
     st.close()
 t = torch.tensor([int(ok)], device="cuda")
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
