@@ -191,7 +191,10 @@ class Params:
     """Scheme parameters shared by every oracle entry point."""
 
     def __init__(self, N, g=2, a=EARTH_RADIUS, omega=EARTH_OMEGA, grav=EARTH_GRAVITY,
-                 axis=(0.0, 0.0, 1.0), limiter="mc", rk="ssprk3", advect_only=False, hs=None):
+                 axis=(0.0, 0.0, 1.0), limiter="mc", rk="ssprk3", advect_only=False, hs=None, tangents=None, halo_fill=None):
+        """``tangents``: optional table of the N + 2g tangents tan(alpha_I) incl. ghosts (default: the periodic
+        continuation); ``halo_fill``: optional replacement ``f(h, u, v) -> (h, u, v)`` for the ghost
+        fill after each stage.  Both are hooks for oracle/seam_study.py; the parity oracle uses neither."""
         if g < 2:
             raise ValueError("the step needs a halo of width g >= 2")
         if limiter not in LIMITERS:
@@ -202,7 +205,8 @@ class Params:
         self.axis = np.asarray(axis, dtype=np.float64)
         self.limiter, self.rk, self.advect_only = limiter, rk, advect_only
         self.delta = 0.5 * np.pi / N
-        t = padded_tangents(N, g)
+        t = padded_tangents(N, g) if tangents is None else np.asarray(tangents, dtype=np.float64)
+        self.halo_fill = halo_fill
         X = t[None, :]
         Y = t[:, None]
         A = 1.0 + X * X
@@ -296,6 +300,8 @@ def rk_stage(p: Params, q0, qs, a, b, dt):
         o = np.zeros_like(xs)
         o[:, c, c] = a * x0[:, c, c] + b * (xs[:, c, c] + dt * dx)
         out.append(o)
+    if p.halo_fill is not None:
+        return p.halo_fill(out[0], out[1], out[2])
     return halo_fill_state(out[0], out[1], out[2], g)
 
 

@@ -122,7 +122,13 @@ def test_fused_diag_can_be_switched_off_and_stage_entry_agrees(built_library):
     d1 = torch.zeros(2, dtype=torch.float64, device="cuda")
     ctx0.step(*dev0, dt, diag=d0)
     ctx1.step(*dev1, dt, diag=d1)
-    assert all(torch.equal(a, b) for a, b in zip(dev0, dev1))        # the state does not depend on who sums
+    # the summing build of the stage kernel is a different instantiation: the compiler contracts a few multiply-adds
+    # differently, so the states agree to rounding (each build is bit-reproducible run to run), not bit for bit
+    for a, b in zip(dev0, dev1):
+        scale = float(b.abs().max())
+        worst = float((a - b).abs().max()) / scale
+        print(f"state with / without fused sums: max difference {worst:.1e} of the field's scale")
+        assert worst <= 1e-14
     a, b = d0.cpu().numpy(), d1.cpu().numpy()
     assert abs(a[0] - b[0]) <= 1e-13 * abs(a[0]) and abs(a[1] - b[1]) <= 1e-12 * abs(a[1])
     # one stage through cs_rk_stage

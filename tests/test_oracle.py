@@ -108,8 +108,9 @@ def test_tc2_is_nearly_steady_and_converges():
             st = orc.step(p, st, dt)
         c = slice(2, 2 + N)
         errs.append(np.sqrt(np.sum(p.sg[c, c] * (st[0][:, c, c] - h0[:, c, c]) ** 2) / np.sum(p.sg[c, c] * h0[:, c, c] ** 2)))
-    # direct-copy halos are first-order at the seams: error at least halves with the mesh
-    assert errs[0] < 5e-3 and errs[1] < 0.62 * errs[0]
+    # direct-copy halos are first-order at the seams (measured order 1.2-1.3): the error falls by more
+    # than 2^0.7 per doubling of the mesh, well short of the 4 a second-order scheme gives (next test)
+    assert errs[0] < 5e-3 and errs[1] < 0.62 * errs[0] and errs[1] > 0.3 * errs[0]
 
 
 def test_tc1_bell_crosses_faces_3_to_4():
@@ -188,3 +189,18 @@ def test_fp32_c_oracle_tracks_the_fp64_one():
     occ.halo_fill(N, g, h, u, v)
     for a, b in zip((h, u, v), ref):
         assert a.dtype == np.float32 and np.array_equal(a, b)
+
+
+def test_seam_study_interpolated_ghosts_are_second_order():
+    """oracle/seam_study.py: with ghost values interpolated to OUR extended grid points (1-D cubic along the
+    neighbour's rows, vectors rotated at the ghost point, metric extended) the same scheme converges at second order
+    on Williamson case 2 -- the reference's "solid 2nd-order method" (deck slide 4) -- but the seam fluxes are no
+    longer single valued and mass drifts at truncation level; the copy halo keeps mass to round-off at first order."""
+    from oracle import seam_study
+    e16, d16, _ = seam_study.run_case(16, "interp", 0.25)
+    e32, d32, _ = seam_study.run_case(32, "interp", 0.25)
+    order = np.log2(e16 / e32)
+    assert order > 1.8, (e16, e32, order)
+    c32, dc32, _ = seam_study.run_case(32, "copy", 0.25)
+    assert e32 < 0.2 * c32                                  # an order of magnitude more accurate at C32 already
+    assert abs(dc32) < 1e-14 and 1e-9 < abs(d32) < 1e-4     # round-off vs truncation-level mass drift
