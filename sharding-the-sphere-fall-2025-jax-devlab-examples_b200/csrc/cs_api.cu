@@ -206,6 +206,8 @@ extern "C" int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double
     // graph replay unless the caller is itself capturing this stream (no nested capture) or opted out
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(s, &cap) != cudaSuccess) cudaGetLastError(), cap = cudaStreamCaptureStatusNone;
+    // a whole-sphere context steps in ONE launch when it can (no graph needed: there is nothing to stitch together)
+    if (cs_step_kernel_eligible(ctx, h, u, v, diag_out)) return cs_launch_step_kernel(ctx, h, u, v, dt, diag_out, s);
     if (ctx->tune.step_graph && cap == cudaStreamCaptureStatusNone) {
         StepGraph* g = find_or_capture(ctx, h, u, v, dt, diag_out);
         if (!g && ctx->pdl) {                             // a driver that cannot capture programmatic edges: plain edges

@@ -195,6 +195,7 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
     tu.fused_halo = env_int("CS_FUSED_HALO", tu.fused_halo);
     tu.step_graph = env_int("CS_STEP_GRAPH", tu.step_graph);
     tu.fused_diag = env_int("CS_FUSED_DIAG", tu.fused_diag);
+    tu.step_kernel = env_int("CS_STEP_KERNEL", tu.step_kernel);
     *out = ctx;
     return CS_OK;
 }

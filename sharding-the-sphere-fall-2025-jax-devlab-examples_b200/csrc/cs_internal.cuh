@@ -45,6 +45,7 @@ struct CsTuning {
     int tma_ring = 6;            // CS_TMA_RING
     int fused_halo = 1;          // CS_FUSED_HALO: 0 vetoes cfg.fused_halo
     int step_graph = 1;          // CS_STEP_GRAPH: 0 = cs_step enqueues its launches instead of replaying a graph
+    int step_kernel = 1;         // CS_STEP_KERNEL: 0 = cs_step never uses the one-launch-per-step kernel
     int fused_diag = 1;          // CS_FUSED_DIAG: 0 = diagnostics of a step by the separate reduction kernel
 };
 
@@ -167,6 +168,9 @@ int cs_launch_halo(cs_ctx* ctx, void* h, void* u, void* v, int nfields_mask, cud
 int cs_launch_stage(cs_ctx* ctx, const void* const q0[3], const void* const qs[3], void* const qout[3],
                     double a, double b, double dt, int part, double* diag_out, int sums_in, cudaStream_t s);   // sums_in: diag_out gets
                                                                           // the sums of the stage input instead of its output
+// one launch per step (cs_step_kernel.cu): whether cs_step may take it for these arguments, and the launch itself
+bool cs_step_kernel_eligible(const cs_ctx* ctx, const void* h, const void* u, const void* v, const double* diag_out);
+int cs_launch_step_kernel(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out, cudaStream_t s);
 int cs_launch_diag(cs_ctx* ctx, const void* h, const void* u, const void* v, double* out, cudaStream_t s);
 int cs_launch_pack(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* sendbuf,
                    cudaStream_t s);

@@ -298,14 +298,13 @@ __device__ __forceinline__ void march_row_update(const StageParams<R>& P, const 
 // SUMS: 0 = none; 1 = the launch also leaves mass / energy of its OUTPUT cells in P.diag_out (K3 fused into K2, new-state
 // semantics; costs registers and ~16 instructions per cell); 2 = of its INPUT cells (taken in march_derive, ~6
 // instructions per cell and no registers: the cheap way to monitor conservation, one stage behind).
-template <typename R, int V, int LIM, int MINB, bool PUSH, bool UNIT = false, int SUMS = 0>
-__global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
-stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant__ MarchGeom G) {
-    const int lane = threadIdx.x & 31;
-    // work items are (tile, strip, chunk) triples, chunk fastest, one per warp: consecutive warps take
-    // neighbouring column chunks of the same strip, and no warp slot idles when nchunks % 4 != 0
-    const int item = blockIdx.x * (CS_MARCH_THREADS / 32) + (threadIdx.x >> 5);
-    if (item >= G.nitems) return;                         // whole warp leaves together
+//
+// march_item is the whole stage for ONE work item (tile, strip, chunk), run by one warp; the two kernels below call it:
+// stage_march_kernel (one stage per launch, one item per warp) and step_march_kernel (a whole time step per launch).
+// PDL: the caller was launched as a programmatic dependent and the state may be touched only after the grid dependency.
+template <typename R, int V, int LIM, bool PUSH, bool UNIT, int SUMS, bool PDL>
+__device__ __forceinline__ void march_item(const StageParams<R>& P, const MarchGeom& G, const int item, const int lane,
+                                           double& dmass, double& denergy2) {
     const int chunk = item % G.nchunks;
     const int strip = (item / G.nchunks) % G.nstrips;
     const int t = item / (G.nchunks * G.nstrips);
@@ -362,14 +361,15 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     // Launched as a programmatic dependent: everything above (indices, metric constants from tables no kernel writes)
     // may run while the previous kernel in the stream drains; the state is touched only after this point.  The
     // trigger lets the next kernel's blocks be scheduled as this grid's blocks retire.
-    cudaGridDependencySynchronize();
-    cudaTriggerProgrammaticLaunchCompletion();
+    if constexpr (PDL) {
+        cudaGridDependencySynchronize();
+        cudaTriggerProgrammaticLaunchCompletion();
+    }
 
     // ---- prologue: rows J0-2 .. J0+1 --------------------------------------------------------
     const int J0 = j0 + g, J1 = j1 + g;
     R hc[V], hp[V], nh[V], uc[V], vc[V], nu[V], nv[V], nt[V];
     R c1m[V], Bnm[V], Gs[V], syc[V];
-    double dmass = 0.0, denergy2 = 0.0;                   // SUMS: this thread's share of the conservation sums
     RowDerived<R, V> Dc;
     R Yc = yt[J0], ayc = ayt[J0];                         // tan(beta) and 1/(1+Y^2) of the current row
     R Yn = yt[J0 + 1], ayn = ayt[J0 + 1];                 // ... and of the next one (loaded a row ahead)
@@ -517,41 +517,187 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
         row(Dn, Dc, J + 1);
     }
     if (J < J1) row(Dc, Dn, J);
+}
 
-    if constexpr (SUMS != 0) {
-        // one (mass, energy) partial per work item; the warp that takes the last ticket adds the partials in index
-        // order, so the result does not depend on which warp finishes when (no floating-point atomics)
-        // SUMS == 1 carries twice the energy density, SUMS == 2 the density itself
-        double pm = dmass * (double)P.darea, pe = denergy2 * ((SUMS == 1 ? 0.5 : 1.0) * (double)P.darea);
+// One (mass, energy) partial per slot (a work item, or a warp of the step kernel); the warp that takes the last ticket
+// adds the partials in index order, so the result does not depend on which warp finishes when (no floating-point
+// atomics).  `scale_e`: SUMS == 1 carries twice the energy density, SUMS == 2 the density itself.
+template <typename R>
+__device__ __forceinline__ void march_finish_sums(const StageParams<R>& P, int slot, int nslots, int lane, double dmass,
+                                                  double denergy2, double scale_e) {
+    double pm = dmass * (double)P.darea, pe = denergy2 * (scale_e * (double)P.darea);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        pm += __shfl_down_sync(0xffffffffu, pm, o);
+        pe += __shfl_down_sync(0xffffffffu, pe, o);
+    }
+    unsigned int ticket = 0;
+    if (lane == 0) {
+        P.partials[2 * slot] = pm;
+        P.partials[2 * slot + 1] = pe;
+        __threadfence();
+        ticket = atomicAdd(P.ticket, 1u);
+    }
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket == (unsigned int)nslots - 1u) {
+        __threadfence();
+        double a = 0.0, b = 0.0;
+        for (int k = lane; k < nslots; k += 32) {
+            a += __ldcg(P.partials + 2 * k);              // other warps wrote these: read through L2, never a stale L1 line
+            b += __ldcg(P.partials + 2 * k + 1);
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
-            pm += __shfl_down_sync(0xffffffffu, pm, o);
-            pe += __shfl_down_sync(0xffffffffu, pe, o);
+            a += __shfl_down_sync(0xffffffffu, a, o);
+            b += __shfl_down_sync(0xffffffffu, b, o);
         }
-        unsigned int ticket = 0;
         if (lane == 0) {
-            P.partials[2 * item] = pm;
-            P.partials[2 * item + 1] = pe;
-            __threadfence();
-            ticket = atomicAdd(P.ticket, 1u);
+            P.diag_out[0] = a, P.diag_out[1] = b;
+            *P.ticket = 0;                                // ready for the next launch on this stream
         }
-        ticket = __shfl_sync(0xffffffffu, ticket, 0);
-        if (ticket == (unsigned int)G.nitems - 1u) {
-            __threadfence();
-            double a = 0.0, b = 0.0;
-            for (int k = lane; k < G.nitems; k += 32) {
-                a += __ldcg(P.partials + 2 * k);          // other warps wrote these: read through L2, never a stale L1 line
-                b += __ldcg(P.partials + 2 * k + 1);
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                a += __shfl_down_sync(0xffffffffu, a, o);
-                b += __shfl_down_sync(0xffffffffu, b, o);
-            }
-            if (lane == 0) {
-                P.diag_out[0] = a, P.diag_out[1] = b;
-                *P.ticket = 0;                            // ready for the next launch on this stream
-            }
+    }
+}
+
+// One stage per launch: one work item per warp, items flattened chunk-fastest into a 1-D grid, so consecutive warps
+// take neighbouring column chunks of the same strip and no warp slot idles when nchunks % 4 != 0.
+template <typename R, int V, int LIM, int MINB, bool PUSH, bool UNIT = false, int SUMS = 0>
+__global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
+stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant__ MarchGeom G) {
+    const int lane = threadIdx.x & 31;
+    const int item = blockIdx.x * (CS_MARCH_THREADS / 32) + (threadIdx.x >> 5);
+    if (item >= G.nitems) return;                         // whole warp leaves together
+    double dmass = 0.0, denergy2 = 0.0;                   // SUMS: this thread's share of the conservation sums
+    march_item<R, V, LIM, PUSH, UNIT, SUMS, true>(P, G, item, lane, dmass, denergy2);
+    if constexpr (SUMS != 0) march_finish_sums<R>(P, item, G.nitems, lane, dmass, denergy2, SUMS == 1 ? 0.5 : 1.0);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CS step kernel: one launch per time step.
+//
+// A step of the one-stage-per-launch path is 6 launches (3 stages, 3 ghost fills): at C1536 fp32 the gaps between
+// them and the short fill kernels cost 30 of 282 microseconds, and on small spheres they are most of the step.  Here
+// one cooperative grid runs all stages: a warp marches its work items, then copies the boundary cells it has just
+// written into the ghost cells of the neighbouring tiles that mirror them (the same index map and signed permutation as
+// the ghost-fill kernel, but only where it matters: edge strips, in a pass after the march so that the marching loop
+// keeps its registers), and the whole grid meets at a barrier before the next stage.  After the last stage the
+// table-driven fill runs once over every ghost cell, so the state the caller gets back has the same ghosts, corner
+// blocks included, as after cs_halo_fill_state.  Needs every neighbour tile on this device (a whole-sphere context).
+// ---------------------------------------------------------------------------------------------------------------
+#include <cooperative_groups.h>
+
+template <typename R>
+struct StepParams {
+    StageParams<R> st[3];
+    int nstages;                     // 2 or 3
+    const int32_t* halo_dst;         // the context's ghost table (all local)
+    const int32_t* halo_src;
+    const uint8_t* halo_code;
+    long long halo_count;
+};
+
+// Boundary cells of one finished work item -> the neighbours' edge ghosts.  All lanes take part: lanes read cells other
+// lanes of the warp wrote (after __syncwarp; through L2, which is where the stores went).
+template <typename R, int V>
+__device__ __forceinline__ void march_push_item(const StageParams<R>& P, const MarchGeom& G, const int item, const int lane) {
+    const int chunk = item % G.nchunks;
+    const int strip = (item / G.nchunks) % G.nstrips;
+    const int t = item / (G.nchunks * G.nstrips);
+    const int n = P.n, g = P.g, m = P.m;
+    const int j0 = G.ylo + strip * G.rows, j1 = min(j0 + G.rows, G.yhi);
+    // interior columns this chunk's output lanes own
+    const int i0 = max(G.xlo, (G.grp0 + chunk * CS_MARCH_OUT_LANES) * V - g);
+    const int i1 = min(G.xhi, (G.grp0 + (chunk + 1) * CS_MARCH_OUT_LANES) * V - g);
+    const unsigned tile = (unsigned)t * m * m;
+    const bool south = j0 < g, north = j1 > n - g, west = i0 < g, east = i1 > n - g;
+    if (!(south || north || west || east)) return;        // most items touch no tile edge
+    __syncwarp();
+    for (int d = 0; d < g; ++d) {
+        if (south && d >= j0 && d < j1) {
+            const PushMap pm = march_push_map<R>(P, t, 1, d);
+            if (pm.code >= 0)
+                for (int i = i0 + lane; i < i1; i += 32) {
+                    const unsigned o = tile + (unsigned)(d + g) * m + i + g;
+                    march_push_store<R>(P, pm, i, __ldcg(P.ho + o), __ldcg(P.uo + o), __ldcg(P.vo + o));
+                }
         }
+        const int jn = n - 1 - d;
+        if (north && jn >= j0 && jn < j1) {
+            const PushMap pm = march_push_map<R>(P, t, 0, d);
+            if (pm.code >= 0)
+                for (int i = i0 + lane; i < i1; i += 32) {
+                    const unsigned o = tile + (unsigned)(jn + g) * m + i + g;
+                    march_push_store<R>(P, pm, i, __ldcg(P.ho + o), __ldcg(P.uo + o), __ldcg(P.vo + o));
+                }
+        }
+        if (west && d >= i0 && d < i1) {
+            const PushMap pm = march_push_map<R>(P, t, 3, d);
+            if (pm.code >= 0)
+                for (int j = j0 + lane; j < j1; j += 32) {
+                    const unsigned o = tile + (unsigned)(j + g) * m + d + g;
+                    march_push_store<R>(P, pm, j, __ldcg(P.ho + o), __ldcg(P.uo + o), __ldcg(P.vo + o));
+                }
+        }
+        const int ie = n - 1 - d;
+        if (east && ie >= i0 && ie < i1) {
+            const PushMap pm = march_push_map<R>(P, t, 2, d);
+            if (pm.code >= 0)
+                for (int j = j0 + lane; j < j1; j += 32) {
+                    const unsigned o = tile + (unsigned)(j + g) * m + ie + g;
+                    march_push_store<R>(P, pm, j, __ldcg(P.ho + o), __ldcg(P.uo + o), __ldcg(P.vo + o));
+                }
+        }
+    }
+}
+
+// UNIT1: the first stage uses the (a, b) = (0, 1) build (fp64); SUMS1: 0, or 2 = the launch also leaves mass / energy
+// of the state the step starts from in st[0].diag_out.
+template <typename R, int V, int LIM, int MINB, bool UNIT1, int SUMS1>
+__global__ void __launch_bounds__(CS_MARCH_THREADS, MINB)
+step_march_kernel(const __grid_constant__ StepParams<R> S, const __grid_constant__ MarchGeom G) {
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const int lane = threadIdx.x & 31;
+    const int warp = blockIdx.x * (CS_MARCH_THREADS / 32) + (threadIdx.x >> 5);
+    const int nwarps = gridDim.x * (CS_MARCH_THREADS / 32);
+    double dmass = 0.0, denergy = 0.0;
+#pragma unroll 1
+    for (int item = warp; item < G.nitems; item += nwarps) {
+        march_item<R, V, LIM, false, UNIT1, SUMS1, false>(S.st[0], G, item, lane, dmass, denergy);
+        march_push_item<R, V>(S.st[0], G, item, lane);
+    }
+    if constexpr (SUMS1 == 2) march_finish_sums<R>(S.st[0], warp, nwarps, lane, dmass, denergy, 1.0);
+    double unused0 = 0.0, unused1 = 0.0;
+    if (S.nstages > 1) {
+        __threadfence();
+        grid.sync();
+#pragma unroll 1
+        for (int item = warp; item < G.nitems; item += nwarps) {
+            march_item<R, V, LIM, false, false, 0, false>(S.st[1], G, item, lane, unused0, unused1);
+            march_push_item<R, V>(S.st[1], G, item, lane);
+        }
+    }
+    if (S.nstages > 2) {
+        __threadfence();
+        grid.sync();
+#pragma unroll 1
+        for (int item = warp; item < G.nitems; item += nwarps) {
+            march_item<R, V, LIM, false, false, 0, false>(S.st[2], G, item, lane, unused0, unused1);
+            march_push_item<R, V>(S.st[2], G, item, lane);
+        }
+    }
+    // every ghost cell of the new state, corner blocks included, exactly as the ghost-fill kernel leaves them
+    __threadfence();
+    grid.sync();
+    const StageParams<R>& L = S.st[S.nstages > 2 ? 2 : S.nstages - 1];
+    R* h = L.ho;                                           // sources are interior cells, targets ghost cells of the same arrays
+    R* u = L.uo;
+    R* v = L.vo;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < S.halo_count; k += (long long)gridDim.x * blockDim.x) {
+        const int32_t d = S.halo_dst[k], s = S.halo_src[k];
+        const int code = S.halo_code[k];
+        const R a = __ldcg(u + s), b = __ldcg(v + s);
+        h[d] = __ldcg(h + s);
+        const R x = (code & 1) ? b : a, y = (code & 1) ? a : b;
+        u[d] = (code & 2) ? -x : x;
+        v[d] = (code & 4) ? -y : y;
     }
 }

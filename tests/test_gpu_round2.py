@@ -285,3 +285,60 @@ def test_halo_with_geometric_rotation_tables(built_library, N, p):
     assert np.abs(gu[dst] - au).max() <= 1e-12 * scale and np.abs(gv[dst] - av).max() <= 1e-12 * scale
     ctx.set_rotation(None)
     ctx.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# one launch per step (step_march_kernel) against the one-stage-per-launch path
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("name,N,p,dtype,rk", [("tc5", 48, 1, np.float64, "ssprk3"), ("tc2", 48, 2, np.float64, "ssprk3"),
+                                                ("galewsky", 96, 1, np.float32, "ssprk3"), ("tc6", 40, 1, np.float64, "ssprk2"),
+                                                ("tc1", 36, 3, np.float32, "ssprk3"), ("tc5", 192, 1, np.float64, "ssprk3")])
+def test_step_kernel_matches_stage_launches(built_library, name, N, p, dtype, rk):
+    """cs_step in ONE cooperative launch (stages separated by grid barriers, edge ghosts pushed by the warps that
+    computed the boundary cells, final table-driven fill) against the six-launch path: same interior to rounding, every
+    ghost cell -- corner blocks included -- a bit-exact copy of its source, same entry-state sums, one kernel per step."""
+    g = 2
+    case = cases.make_case(name, N)
+    kw = dict(tiles_per_edge=p, halo=g, dtype=dtype, rk=rk, advect_only=case.advect_only, axis=case.axis,
+              tangents=orc.centre_tangents(N), sums_of_entry_state=True)
+    os.environ["CS_STEP_KERNEL"] = "0"
+    try:
+        ctx0 = api.Context(N, **kw)
+    finally:
+        del os.environ["CS_STEP_KERNEL"]
+    ctx1 = api.Context(N, **kw)
+    par = orc.Params(N, g, axis=case.axis, rk=rk, advect_only=case.advect_only, hs=case.hs)
+    ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
+    dev0 = [torch.from_numpy(orc.faces_to_tiles(x, p, g).astype(dtype)).cuda() for x in ref]
+    dev1 = [x.clone() for x in dev0]
+    if case.hs is not None:
+        for c in (ctx0, ctx1):
+            c.set_topography(torch.from_numpy(orc.faces_to_tiles(par.hs, p, g).astype(dtype)).cuda())
+    dt = cases.stable_dt(case, 0.5)
+    d0 = torch.zeros(2, dtype=torch.float64, device="cuda")
+    d1 = torch.zeros(2, dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        ctx0.step(*dev0, dt, diag=d0)
+    l0 = ctx1.launches
+    for _ in range(3):
+        ctx1.step(*dev1, dt, diag=d1)
+    assert ctx1.launches - l0 == 3, "expected one launch per step"
+    tol = 1e-13 if dtype is np.float64 else 2e-6
+    for a, b in zip(dev0, dev1):
+        scale = float(a.abs().max())
+        assert float((a - b).abs().max()) <= tol * scale
+    # ghosts of the result: what the table-driven fill gives for this interior, bit for bit
+    again = [x.clone() for x in dev1]
+    ctx1.halo_fill_state(*again)
+    assert all(torch.equal(a, b) for a, b in zip(again, dev1))
+    a, b = d0.cpu().numpy(), d1.cpu().numpy()
+    st = 1e-12 if dtype is np.float64 else 1e-7
+    assert np.all(np.abs(a - b) <= st * np.abs(a)), (a, b)
+    if dtype is np.float64:                                # and against the oracle
+        for _ in range(3):
+            ref = orc.step(par, ref, dt)
+        got = orc.tiles_to_faces(dev1[0].cpu().numpy(), p, g)
+        c = slice(g, g + N)
+        assert np.linalg.norm(got[:, c, c] - ref[0][:, c, c]) <= 1e-13 * np.linalg.norm(ref[0][:, c, c])
+    ctx0.close(), ctx1.close()
