@@ -14,7 +14,7 @@
  *     exception: the first cs_step for a new (h, u, v, dt, diag_out) combination captures and
  *     instantiates a CUDA graph (creates a stream, allocates graph memory; CS_STEP_GRAPH=0 opts out);
  *   - the set-up calls synchronise the device and/or allocate: cs_ctx_create, cs_ctx_destroy,
- *     cs_halo_set_rotation, cs_halo_plan, and cs_step_host[_batch] (which own their copies);
+ *     cs_halo_set_rotation, cs_halo_set_interp, cs_halo_plan, and cs_step_host[_batch] (which own their copies);
  *   - every call runs on the context's device and restores the calling thread's current CUDA
  *     device before it returns;
  *   - return value 0 = success, negative = CS_E_* below; the text of the last
@@ -159,6 +159,23 @@ CS_API int cs_halo_fill_state(cs_ctx* ctx, void* h, void* u, void* v, void* stre
 CS_API int cs_halo_set_rotation(cs_ctx* ctx, const double* rot, size_t n_ghost);
 
 /*
+ * Optional second-order ghosts: instead of copying the neighbour's cell, every ghost cell becomes the value at the
+ * point of OUR extended grid, ((w0 s0 + w1 s1) + w2 s2) + w3 s3 over four interior cells of the neighbour (1-D Lagrange
+ * interpolation along its row at the same depth), vectors then through the 2 x 2 `rot` at that point -- each product
+ * and sum rounded on its own, so a CPU evaluation in the same order is bit-identical.  Host tables, one row per ghost
+ * cell, any order: dst [n], src [n][4] (element offsets into a field), w [n][4], rot [n][4] row-major, all fp64;
+ * tangents (may be NULL) = N + 2 halo tangents replacing the context's periodic table, so that ghost cells carry the
+ * metric of the extended chart.  cubesphere.geometry.seam_interp_tables builds all five.  dst == NULL restores the
+ * plain copy and the periodic metric.  Whole-sphere contexts only.  Trade-off: second order at the
+ * seams instead of first, but seam fluxes are no longer single valued, so mass drifts at truncation level
+ * (1e-7 per day at C96) instead of round-off.  Synchronises the device; allocates.
+ * Replaces: nothing in the reference (its halo is the plain copy, PY:183-195); the deck's "solid 2nd-order method"
+ * (slide 4) is what this option delivers across seams.
+ */
+CS_API int cs_halo_set_interp(cs_ctx* ctx, size_t n_ghost, const int64_t* dst, const int64_t* src, const double* w,
+                       const double* rot, const double* tangents);
+
+/*
  * Ghost-cell table of the context, for callers that want to build rotation
  * tables: writes up to cap entries of (dst_offset, src_offset, code) and returns
  * the ghost-cell count in *n_ghost.  Offsets are element offsets into a field of
@@ -297,6 +314,14 @@ CS_API int cs_diagnostics_noalloc(int dtype, int N, int tiles_per_edge, int halo
  * length was odd or halo < 2.  Either pointer may be NULL.  Replaces: nothing (bookkeeping).
  */
 CS_API int cs_stage_kernel_info(const cs_ctx* ctx, int32_t* last_variant, int64_t* naive_fallbacks);
+
+/*
+ * Tuning aid.  With CS_STEP_DEBUG=16 in the environment when the context is created, the one-launch-per-step kernel
+ * records nanosecond time stamps per thread block (start; end of each stage's march; release from each grid barrier;
+ * end of the final ghost fill): out_host receives [max_blocks][8] values of the last launch.  Synchronises the device.
+ * Replaces: nothing (profiling).
+ */
+CS_API int cs_step_kernel_trace(cs_ctx* ctx, int max_blocks, unsigned long long* out_host);
 
 /* Number of kernels this library has launched on ctx since creation (bench bookkeeping). */
 CS_API int64_t cs_launch_count(const cs_ctx* ctx);

@@ -52,6 +52,28 @@ int upload_table(cs_ctx* ctx, void** dptr, const std::vector<double>& v) {
     return CS_OK;
 }
 
+}  // namespace
+
+// device copies of the tangent table ctx->xt (N + 2g entries) in the state's dtype and in fp64, and of 1 / (1 + X^2)
+int cs_upload_metric(cs_ctx* ctx) {
+    std::vector<double> ainv(ctx->xt.size());
+    for (size_t I = 0; I < ctx->xt.size(); ++I) ainv[I] = 1.0 / (1.0 + ctx->xt[I] * ctx->xt[I]);
+    for (void** q : {&ctx->d_xt, &ctx->d_ainv, (void**)&ctx->d_xt64})
+        if (*q) cudaFree(*q), *q = nullptr;
+    int rc;
+    if ((rc = upload_table<double>(ctx, (void**)&ctx->d_xt64, ctx->xt))) return rc;
+    if (ctx->dtype == CS_F64) {
+        if ((rc = upload_table<double>(ctx, &ctx->d_xt, ctx->xt))) return rc;
+        if ((rc = upload_table<double>(ctx, &ctx->d_ainv, ainv))) return rc;
+    } else {
+        if ((rc = upload_table<float>(ctx, &ctx->d_xt, ctx->xt))) return rc;
+        if ((rc = upload_table<float>(ctx, &ctx->d_ainv, ainv))) return rc;
+    }
+    return CS_OK;
+}
+
+namespace {
+
 int build_tables(cs_ctx* ctx, const double* tangents) {
     const int N = ctx->N, g = ctx->g;
     std::vector<double> x(N);
@@ -63,21 +85,11 @@ int build_tables(cs_ctx* ctx, const double* tangents) {
         for (int i = 0; i < N / 2; ++i) x[i] = -x[N - 1 - i];   // exactly antisymmetric
         if (N % 2) x[N / 2] = 0.0;
     }
+    ctx->x_base = x;
     ctx->xt.resize(N + 2 * g);
-    std::vector<double> ainv(N + 2 * g);
-    for (int I = 0; I < N + 2 * g; ++I) {
-        ctx->xt[I] = x[((I - g) % N + N) % N];                  // periodic continuation
-        ainv[I] = 1.0 / (1.0 + ctx->xt[I] * ctx->xt[I]);
-    }
+    for (int I = 0; I < N + 2 * g; ++I) ctx->xt[I] = x[((I - g) % N + N) % N];      // periodic continuation
     int rc;
-    if ((rc = upload_table<double>(ctx, (void**)&ctx->d_xt64, ctx->xt))) return rc;
-    if (ctx->dtype == CS_F64) {
-        if ((rc = upload_table<double>(ctx, &ctx->d_xt, ctx->xt))) return rc;
-        if ((rc = upload_table<double>(ctx, &ctx->d_ainv, ainv))) return rc;
-    } else {
-        if ((rc = upload_table<float>(ctx, &ctx->d_xt, ctx->xt))) return rc;
-        if ((rc = upload_table<float>(ctx, &ctx->d_ainv, ainv))) return rc;
-    }
+    if ((rc = cs_upload_metric(ctx))) return rc;
     static const double FRd[6][3][3] = {
         {{0, 0, 1}, {1, 0, 0}, {0, 1, 0}},   {{0, 1, 0}, {-1, 0, 0}, {0, 0, 1}},
         {{-1, 0, 0}, {0, -1, 0}, {0, 0, 1}}, {{0, -1, 0}, {1, 0, 0}, {0, 0, 1}},
@@ -196,6 +208,7 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
     tu.step_graph = env_int("CS_STEP_GRAPH", tu.step_graph);
     tu.fused_diag = env_int("CS_FUSED_DIAG", tu.fused_diag);
     tu.step_kernel = env_int("CS_STEP_KERNEL", tu.step_kernel);
+    tu.step_debug = env_int("CS_STEP_DEBUG", tu.step_debug);
     *out = ctx;
     return CS_OK;
 }
@@ -215,7 +228,7 @@ extern "C" int cs_ctx_destroy(cs_ctx* ctx) {
         if (ctx->pipe.state[1][k]) cudaFree(ctx->pipe.state[1][k]);
     if (ctx->pipe.diag) cudaFree(ctx->pipe.diag);
     if (ctx->pipe.diag_pinned) cudaFreeHost(ctx->pipe.diag_pinned);
-    void* ptrs[] = {ctx->d_xt, ctx->d_ainv, ctx->d_xt64, ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, ctx->d_rot, ctx->d_push,
+    void* ptrs[] = {ctx->d_xt, ctx->d_ainv, ctx->d_xt64, ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, ctx->d_rot, ctx->d_push, ctx->d_interp_dst, ctx->d_interp_src, ctx->d_interp_w, ctx->d_interp_rot,
                     ctx->d_send_src, ctx->d_recv_dst, ctx->d_recv_code, ctx->d_send_off, ctx->d_recv_off, ctx->qa[0], ctx->qa[1], ctx->qa[2],
                     ctx->qb[0], ctx->qb[1], ctx->qb[2], ctx->topo, ctx->host_state[0], ctx->host_state[1], ctx->host_state[2], ctx->d_partials, ctx->d_diag, ctx->d_ticket};
     for (void* q : ptrs)

@@ -51,6 +51,34 @@ halo_fill_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const 
     }
 }
 
+// Interpolated ghosts (cs_halo_set_interp): ghost = ((w0 s0 + w1 s1) + w2 s2) + w3 s3 over four interior cells of the
+// neighbour's row at the same depth, vectors then through a 2 x 2; every product and sum is rounded on its own (no FMA
+// contraction), so a CPU evaluation in the same order gives the same bits.
+template <typename R>
+__device__ __forceinline__ R interp4(const R* __restrict__ f, const int4 s, const R w0, const R w1, const R w2, const R w3) {
+    return add_rn(add_rn(add_rn(mul_rn(w0, f[s.x]), mul_rn(w1, f[s.y])), mul_rn(w2, f[s.z])), mul_rn(w3, f[s.w]));
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256)
+halo_interp_kernel(R* h, R* u, R* v, const int32_t* __restrict__ dst, const int4* __restrict__ src, const R* __restrict__ w,
+                   const R* __restrict__ rot, int64_t count, int mask) {
+    cudaGridDependencySynchronize();
+    cudaTriggerProgrammaticLaunchCompletion();
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < count; k += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t d = dst[k];
+        const int4 s = src[k];
+        const R w0 = w[4 * k], w1 = w[4 * k + 1], w2 = w[4 * k + 2], w3 = w[4 * k + 3];
+        if (mask & 1) h[d] = interp4<R>(h, s, w0, w1, w2, w3);
+        if (mask & 2) {
+            const R a = interp4<R>(u, s, w0, w1, w2, w3), b = interp4<R>(v, s, w0, w1, w2, w3);
+            const R* r = rot + 4 * k;
+            u[d] = add_rn(mul_rn(r[0], a), mul_rn(r[1], b));
+            v[d] = add_rn(mul_rn(r[2], a), mul_rn(r[3], b));
+        }
+    }
+}
+
 // sendbuf layout: for each peer block [field][cell]; the caller slices it per peer
 template <typename R>
 __global__ void __launch_bounds__(256)
@@ -100,6 +128,19 @@ int grid_for(const cs_ctx* ctx, int64_t count) {
 }  // namespace
 
 int cs_launch_halo(cs_ctx* ctx, void* h, void* u, void* v, int mask, cudaStream_t s) {
+    if (ctx->d_interp_dst) {
+        const dim3 grid(grid_for(ctx, ctx->n_interp)), block(256);
+        if (ctx->dtype == CS_F64)
+            CS_CUDA(ctx, cs_launch_dependent(halo_interp_kernel<double>, grid, block, 0, s, ctx->pdl, (double*)h, (double*)u, (double*)v,
+                                             ctx->d_interp_dst, ctx->d_interp_src, (const double*)ctx->d_interp_w,
+                                             (const double*)ctx->d_interp_rot, (int64_t)ctx->n_interp, mask));
+        else
+            CS_CUDA(ctx, cs_launch_dependent(halo_interp_kernel<float>, grid, block, 0, s, ctx->pdl, (float*)h, (float*)u, (float*)v,
+                                             ctx->d_interp_dst, ctx->d_interp_src, (const float*)ctx->d_interp_w,
+                                             (const float*)ctx->d_interp_rot, (int64_t)ctx->n_interp, mask));
+        ctx->launches++;
+        return CS_OK;
+    }
     if (ctx->n_local == 0) return CS_OK;
     const dim3 grid(grid_for(ctx, ctx->n_local)), block(256);
     if (ctx->dtype == CS_F64)
@@ -169,6 +210,60 @@ extern "C" int cs_halo_set_rotation(cs_ctx* ctx, const double* rot, size_t n_gho
     } else {
         std::vector<float> tmp(rot, rot + count);
         CS_CUDA(ctx, cudaMemcpy(ctx->d_rot, tmp.data(), count * 4, cudaMemcpyHostToDevice));
+    }
+    return CS_OK;
+}
+
+extern "C" int cs_halo_set_interp(cs_ctx* ctx, size_t n_ghost, const int64_t* dst, const int64_t* src, const double* w,
+                                  const double* rot, const double* tangents) {
+    if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_halo_set_interp: NULL context");
+    CS_ON_DEVICE(ctx, ctx->device);
+    CS_CUDA(ctx, cudaDeviceSynchronize());
+    cs_drop_graphs(ctx);
+    for (void** q : {(void**)&ctx->d_interp_dst, (void**)&ctx->d_interp_src, &ctx->d_interp_w, &ctx->d_interp_rot})
+        if (*q) cudaFree(*q), *q = nullptr;
+    ctx->n_interp = 0;
+    const int N = ctx->N, g = ctx->g;
+    if (!dst) {                                           // back to the plain copy and the periodic metric
+        for (int I = 0; I < N + 2 * g; ++I) ctx->xt[I] = ctx->x_base[((I - g) % N + N) % N];
+        return cs_upload_metric(ctx);
+    }
+    if (!src || !w || !rot) return cs_fail(ctx, CS_E_INVALID, "cs_halo_set_interp: NULL table");
+    if (ctx->T != ctx->T_all)
+        return cs_fail(ctx, CS_E_UNSUPPORTED, "cs_halo_set_interp: interpolated ghosts need a context that owns every tile "
+                                              "(the four sources of a ghost cell would live on other devices)");
+    if (n_ghost != ctx->halo.size())
+        return cs_fail(ctx, CS_E_INVALID, "cs_halo_set_interp: %zu rows, the context has %zu ghost cells", n_ghost, ctx->halo.size());
+    const int64_t elems = (int64_t)ctx->field_elems;
+    std::vector<int32_t> d32(n_ghost);
+    std::vector<int4> s4(n_ghost);
+    for (size_t k = 0; k < n_ghost; ++k) {
+        const int64_t* q = src + 4 * k;
+        if (dst[k] < 0 || dst[k] >= elems || q[0] < 0 || q[0] >= elems || q[1] < 0 || q[1] >= elems || q[2] < 0 || q[2] >= elems ||
+            q[3] < 0 || q[3] >= elems)
+            return cs_fail(ctx, CS_E_INVALID, "cs_halo_set_interp: row %zu has an offset outside the field", k);
+        d32[k] = (int32_t)dst[k];
+        s4[k] = make_int4((int)q[0], (int)q[1], (int)q[2], (int)q[3]);
+    }
+    const size_t count = n_ghost * 4;
+    if (cudaMalloc((void**)&ctx->d_interp_dst, n_ghost * sizeof(int32_t)) != cudaSuccess ||
+        cudaMalloc((void**)&ctx->d_interp_src, n_ghost * sizeof(int4)) != cudaSuccess ||
+        cudaMalloc(&ctx->d_interp_w, count * ctx->esize) != cudaSuccess || cudaMalloc(&ctx->d_interp_rot, count * ctx->esize) != cudaSuccess)
+        return cs_fail(ctx, CS_E_NOMEM, "cs_halo_set_interp: cudaMalloc failed");
+    CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_dst, d32.data(), n_ghost * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_src, s4.data(), n_ghost * sizeof(int4), cudaMemcpyHostToDevice));
+    if (ctx->dtype == CS_F64) {
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_w, w, count * 8, cudaMemcpyHostToDevice));
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_rot, rot, count * 8, cudaMemcpyHostToDevice));
+    } else {
+        std::vector<float> tw(w, w + count), tr(rot, rot + count);
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_w, tw.data(), count * 4, cudaMemcpyHostToDevice));
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_rot, tr.data(), count * 4, cudaMemcpyHostToDevice));
+    }
+    ctx->n_interp = (int64_t)n_ghost;
+    if (tangents) {
+        for (int I = 0; I < N + 2 * g; ++I) ctx->xt[I] = tangents[I];
+        return cs_upload_metric(ctx);
     }
     return CS_OK;
 }

@@ -45,7 +45,9 @@ struct CsTuning {
     int tma_ring = 6;            // CS_TMA_RING
     int fused_halo = 1;          // CS_FUSED_HALO: 0 vetoes cfg.fused_halo
     int step_graph = 1;          // CS_STEP_GRAPH: 0 = cs_step enqueues its launches instead of replaying a graph
-    int step_kernel = 1;         // CS_STEP_KERNEL: 0 = cs_step never uses the one-launch-per-step kernel
+    int step_debug = 0;          // CS_STEP_DEBUG: timing experiments on the step kernel (wrong results)
+    int step_kernel = 0;         // CS_STEP_KERNEL: 1 = cs_step uses the one-launch-per-step kernel where it can (measured
+                                 // slower than the replayed graph of stage launches at every size: DESIGN.md 4.2)
     int fused_diag = 1;          // CS_FUSED_DIAG: 0 = diagnostics of a step by the separate reduction kernel
 };
 
@@ -76,6 +78,13 @@ struct cs_ctx {
     int32_t* d_halo_src = nullptr;
     uint8_t* d_halo_code = nullptr;
     void* d_rot = nullptr;                       // optional [n_local][4] rotation (state dtype)
+    // optional interpolated ghosts (cs_halo_set_interp): every ghost = sum of 4 weighted interior cells, then a 2 x 2
+    int64_t n_interp = 0;
+    int32_t* d_interp_dst = nullptr;             // [n_interp]
+    int4* d_interp_src = nullptr;                // [n_interp] four source offsets
+    void* d_interp_w = nullptr;                  // [n_interp][4] weights (state dtype)
+    void* d_interp_rot = nullptr;                // [n_interp][4] row-major 2 x 2 (state dtype)
+    std::vector<double> x_base;                  // the N centre tangents the context was created with
     int4* d_push = nullptr;                      // [T][4] (dst local tile or -1, dst edge, reverse, code)
     bool push_complete = false;                  // every neighbour tile is local
     bool stage_pushed = false;                   // the last stage launch stored the edge ghosts itself
@@ -161,6 +170,7 @@ struct SeamInfo { int fb, eb, rev, code; };
 SeamInfo cs_seam(int face, int edge);            // edge: 0 N, 1 S, 2 E, 3 W
 void cs_resolve(int face, int64_t J, int64_t I, int N, int* fb, int64_t* Jb, int64_t* Ib, int* code);
 int cs_build_halo(cs_ctx* ctx);
+int cs_upload_metric(cs_ctx* ctx);               // (re)build the device tangent tables from ctx->xt
 int cs_build_peer_plan(cs_ctx* ctx, int n_peers, const int32_t* tb, const int32_t* tc);
 
 // kernel launchers (cs_halo.cu, cs_stage.cu, cs_diag.cu)

@@ -209,7 +209,7 @@ int launch_lim(cs_ctx* ctx, const StageParams<R>& P0, int part, double* diag_out
     }
     StageParams<R> Q = P;
     ctx->stage_pushed = false;
-    if (part == 2 && ctx->cfg.fused_halo && ctx->push_complete && ctx->d_push && !ctx->d_rot && ctx->tune.fused_halo) {
+    if (part == 2 && ctx->cfg.fused_halo && ctx->push_complete && ctx->d_push && !ctx->d_rot && !ctx->d_interp_dst && ctx->tune.fused_halo) {
         Q.push = ctx->d_push;
         ctx->stage_pushed = true;   // the caller can skip the ghost-fill launch (corner blocks are not refreshed)
     }

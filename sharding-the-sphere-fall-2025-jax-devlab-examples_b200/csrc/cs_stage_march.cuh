@@ -593,7 +593,20 @@ struct StepParams {
     const int32_t* halo_src;
     const uint8_t* halo_code;
     long long halo_count;
+    int debug;                       // CS_STEP_DEBUG (timing experiments only): 1 no push, 2 no final fill, 4 no barriers,
+                                     // 8 first stage only, 16 record the trace below
+    unsigned long long* trace;       // [gridDim.x][8] globaltimer at: start, end of march 1, 2, 3, after each barrier
 };
+
+__device__ __forceinline__ unsigned long long cs_globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define CS_STEP_TRACE(slot)                                                                  \
+    do {                                                                                     \
+        if ((S.debug & 16) && threadIdx.x == 0) S.trace[blockIdx.x * 8 + (slot)] = cs_globaltimer(); \
+    } while (0)
 
 // Boundary cells of one finished work item -> the neighbours' edge ghosts.  All lanes take part: lanes read cells other
 // lanes of the warp wrote (after __syncwarp; through L2, which is where the stores went).
@@ -659,34 +672,45 @@ step_march_kernel(const __grid_constant__ StepParams<R> S, const __grid_constant
     const int warp = blockIdx.x * (CS_MARCH_THREADS / 32) + (threadIdx.x >> 5);
     const int nwarps = gridDim.x * (CS_MARCH_THREADS / 32);
     double dmass = 0.0, denergy = 0.0;
+    CS_STEP_TRACE(0);
 #pragma unroll 1
     for (int item = warp; item < G.nitems; item += nwarps) {
         march_item<R, V, LIM, false, UNIT1, SUMS1, false>(S.st[0], G, item, lane, dmass, denergy);
-        march_push_item<R, V>(S.st[0], G, item, lane);
+        if (!(S.debug & 1)) march_push_item<R, V>(S.st[0], G, item, lane);
     }
     if constexpr (SUMS1 == 2) march_finish_sums<R>(S.st[0], warp, nwarps, lane, dmass, denergy, 1.0);
     double unused0 = 0.0, unused1 = 0.0;
-    if (S.nstages > 1) {
+    __syncthreads();
+    CS_STEP_TRACE(1);
+    if (S.nstages > 1 && !(S.debug & 8)) {
         __threadfence();
-        grid.sync();
+        if (!(S.debug & 4)) grid.sync();
+        CS_STEP_TRACE(2);
 #pragma unroll 1
         for (int item = warp; item < G.nitems; item += nwarps) {
             march_item<R, V, LIM, false, false, 0, false>(S.st[1], G, item, lane, unused0, unused1);
-            march_push_item<R, V>(S.st[1], G, item, lane);
+            if (!(S.debug & 1)) march_push_item<R, V>(S.st[1], G, item, lane);
         }
     }
-    if (S.nstages > 2) {
+    __syncthreads();
+    CS_STEP_TRACE(3);
+    if (S.nstages > 2 && !(S.debug & 8)) {
         __threadfence();
-        grid.sync();
+        if (!(S.debug & 4)) grid.sync();
+        CS_STEP_TRACE(4);
 #pragma unroll 1
         for (int item = warp; item < G.nitems; item += nwarps) {
             march_item<R, V, LIM, false, false, 0, false>(S.st[2], G, item, lane, unused0, unused1);
-            march_push_item<R, V>(S.st[2], G, item, lane);
+            if (!(S.debug & 1)) march_push_item<R, V>(S.st[2], G, item, lane);
         }
     }
     // every ghost cell of the new state, corner blocks included, exactly as the ghost-fill kernel leaves them
+    __syncthreads();
+    CS_STEP_TRACE(5);
+    if (S.debug & 2) return;
     __threadfence();
-    grid.sync();
+    if (!(S.debug & 4)) grid.sync();
+    CS_STEP_TRACE(6);
     const StageParams<R>& L = S.st[S.nstages > 2 ? 2 : S.nstages - 1];
     R* h = L.ho;                                           // sources are interior cells, targets ghost cells of the same arrays
     R* u = L.uo;
@@ -700,4 +724,6 @@ step_march_kernel(const __grid_constant__ StepParams<R> S, const __grid_constant
         u[d] = (code & 2) ? -x : x;
         v[d] = (code & 4) ? -y : y;
     }
+    __syncthreads();
+    CS_STEP_TRACE(7);
 }

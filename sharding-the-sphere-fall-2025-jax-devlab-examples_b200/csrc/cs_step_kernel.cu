@@ -65,6 +65,8 @@ int launch_step_typed(cs_ctx* ctx, void* h, void* u, void* v, double dt, const d
     }
     for (int k = ns; k < 3; ++k) S.st[k] = S.st[ns - 1];
     S.nstages = ns;
+    S.debug = ctx->tune.step_debug;
+    S.trace = reinterpret_cast<unsigned long long*>(ctx->d_partials + 4 * (size_t)ctx->partial_cap);   // the reduction kernel's region
     S.halo_dst = ctx->d_halo_dst, S.halo_src = ctx->d_halo_src, S.halo_code = ctx->d_halo_code, S.halo_count = ctx->n_local;
     switch (ctx->cfg.limiter) {
         case CS_LIM_NONE: return launch_step_lim<R, CS_LIM_NONE>(ctx, S, diag_out, s);
@@ -79,7 +81,7 @@ bool cs_step_kernel_eligible(const cs_ctx* ctx, const void* h, const void* u, co
     if (!ctx->tune.step_kernel) return false;
     if (ctx->cfg.kernel != CS_KERNEL_AUTO && ctx->cfg.kernel != CS_KERNEL_MARCH) return false;
     if (ctx->cfg.rk != CS_RK_SSPRK2 && ctx->cfg.rk != CS_RK_SSPRK3) return false;
-    if (ctx->T != ctx->T_all || !ctx->push_complete || !ctx->d_push || ctx->d_rot) return false;
+    if (ctx->T != ctx->T_all || !ctx->push_complete || !ctx->d_push || ctx->d_rot || ctx->d_interp_dst) return false;
     if ((int64_t)ctx->halo.size() != ctx->n_local) return false;
     if (diag_out && !ctx->cfg.sums_of_entry_state) return false;       // sums of the NEW state: the last-stage build
     if (diag_out && !ctx->tune.fused_diag) return false;
@@ -102,4 +104,15 @@ int cs_launch_step_kernel(cs_ctx* ctx, void* h, void* u, void* v, double dt, dou
     ctx->last_stage_kernel = CS_KERNEL_MARCH;
     if (ctx->dtype == CS_F64) return launch_step_typed<double>(ctx, h, u, v, dt, pairs, ns, diag_out, s);
     return launch_step_typed<float>(ctx, h, u, v, dt, pairs, ns, diag_out, s);
+}
+
+// Tuning aid (CS_STEP_DEBUG=16): per-block globaltimer stamps of the last step-kernel launch, [blocks][8].
+extern "C" int cs_step_kernel_trace(cs_ctx* ctx, int max_blocks, unsigned long long* out_host) {
+    if (!ctx || !out_host || max_blocks < 1) return cs_fail(ctx, CS_E_INVALID, "cs_step_kernel_trace: bad argument");
+    if ((int64_t)max_blocks * 8 > 2 * (int64_t)ctx->partial_cap) return cs_fail(ctx, CS_E_INVALID, "cs_step_kernel_trace: too many blocks");
+    CS_ON_DEVICE(ctx, ctx->device);
+    CS_CUDA(ctx, cudaDeviceSynchronize());
+    CS_CUDA(ctx, cudaMemcpy(out_host, ctx->d_partials + 4 * (size_t)ctx->partial_cap, (size_t)max_blocks * 8 * sizeof(unsigned long long),
+                            cudaMemcpyDeviceToHost));
+    return CS_OK;
 }

@@ -43,6 +43,8 @@ _PROTOTYPES = {
     "cs_halo_fill_vector": (C.c_int, [_VP, _VP, _VP, _VP]),
     "cs_halo_fill_state": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
     "cs_halo_set_rotation": (C.c_int, [_VP, C.POINTER(C.c_double), C.c_size_t]),
+    "cs_halo_set_interp": (C.c_int, [_VP, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_double),
+                                     C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "cs_halo_table_info": (C.c_int, [_VP, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                      C.POINTER(C.c_int32), C.POINTER(C.c_size_t)]),
     "cs_set_topography": (C.c_int, [_VP, _VP, _VP]),
@@ -59,6 +61,7 @@ _PROTOTYPES = {
     "cs_halo_pack": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP, _VP]),
     "cs_halo_unpack": (C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_launch_count": (C.c_int64, [_VP]),
+    "cs_step_kernel_trace": (C.c_int, [_VP, C.c_int, C.POINTER(C.c_uint64)]),
     "cs_stage_kernel_info": (C.c_int, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),
     "cs_diagnostics_noalloc": (C.c_int, [C.c_int] * 6 + [C.c_double, C.c_double, _VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
 }

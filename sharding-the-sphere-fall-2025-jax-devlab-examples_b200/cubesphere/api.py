@@ -338,6 +338,30 @@ class Context:
         rot = np.ascontiguousarray(rot, dtype=np.float64).reshape(-1, 4)
         self._check(self._lib.cs_halo_set_rotation(self._h, rot.ctypes.data_as(C.POINTER(C.c_double)), rot.shape[0]))
 
+    def set_halo_interpolation(self, tables):
+        """Install (or clear with None) second-order ghosts: ``tables`` = ``geometry.seam_interp_tables(N, g, p)``
+        (keys dst, src [n, 4], w [n, 4], rot [n, 2, 2], tangents).  Fill ghosts again afterwards; a topography set
+        earlier has to be set again too (its ghosts and the metric change).  See ``cs_halo_set_interp``."""
+        if tables is None:
+            self._check(self._lib.cs_halo_set_interp(self._h, 0, None, None, None, None, None))
+            return
+        dst = np.ascontiguousarray(tables["dst"], dtype=np.int64)
+        src = np.ascontiguousarray(tables["src"], dtype=np.int64).reshape(-1, 4)
+        w = np.ascontiguousarray(tables["w"], dtype=np.float64).reshape(-1, 4)
+        rot = np.ascontiguousarray(tables["rot"], dtype=np.float64).reshape(-1, 4)
+        tang = tables.get("tangents")
+        tp = None
+        if tang is not None:
+            tang = np.ascontiguousarray(tang, dtype=np.float64)
+            if tang.shape != (self.N + 2 * self.g,):
+                raise ValueError(f"tangents must have shape ({self.N + 2 * self.g},)")
+            tp = tang.ctypes.data_as(C.POINTER(C.c_double))
+        if not (dst.shape[0] == src.shape[0] == w.shape[0] == rot.shape[0]):
+            raise ValueError("dst, src, w, rot must have one row per ghost cell")
+        i64, f64 = C.POINTER(C.c_int64), C.POINTER(C.c_double)
+        self._check(self._lib.cs_halo_set_interp(self._h, dst.shape[0], dst.ctypes.data_as(i64), src.ctypes.data_as(i64),
+                                                 w.ctypes.data_as(f64), rot.ctypes.data_as(f64), tp))
+
     # -- step -----------------------------------------------------------------
     def set_topography(self, hs):
         if hs is None:

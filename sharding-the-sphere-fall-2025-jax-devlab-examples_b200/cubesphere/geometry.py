@@ -260,3 +260,96 @@ def seam_rotation_tables(N, g, p=1, kind="contravariant", a=EARTH_RADIUS, table=
     sx = t[(r % p) * n + tab["src_i"] - g]
     sy = t[(r // p) * n + tab["src_j"] - g]
     return seam_rotation(dst_face, src_face, sx, sy, kind, a)
+
+
+# ----------------------------------------------------------------------------
+# second-order ghosts: values at OUR extended grid points  (option; the default halo is the reference's plain copy)
+# ----------------------------------------------------------------------------
+
+def extended_tangents(N: int, g: int) -> np.ndarray:
+    """tan(alpha_I) for I = -g .. N+g-1 with the chart simply continued past +-pi/4 (N + 2g entries): the metric a
+    ghost cell has when it is a point of OUR grid, as opposed to :func:`padded_tangents` (a copy of the neighbour's)."""
+    x = np.tan(-0.25 * np.pi + (np.arange(-g, N + g) + 0.5) * (0.5 * np.pi / N))
+    x[g:g + N] = centre_tangents(N)
+    return x
+
+
+def seam_interp_tables(N, g, p=1, points=4, a=EARTH_RADIUS, table=None):
+    """Tables for ghost values at the points of our own extended grid (Putman & Lin 2007 style), which make the
+    scheme second order at the seams where the plain copy is first order -- at the price of seam fluxes that are no
+    longer single valued (mass drifts at truncation level).  See DESIGN.md 3.5 and oracle/seam_study.py.
+
+    On the equiangular grid a ghost point at depth d lies exactly on the neighbour's coordinate line at depth d, so one
+    1-D Lagrange interpolation (``points`` nodes, one-sided next to the cube corners so that only interior cells are
+    read) along that line gives the value; vectors are interpolated component-wise in the neighbour's chart and then
+    re-expressed in ours by the 2 x 2 matrix of :func:`seam_rotation` at the ghost point.
+
+    Returns a dict, one row per ghost cell in the order of ``table`` (default :func:`topology.build_halo_table`):
+      ``dst`` [n] element offsets, ``src`` [n, 4] element offsets, ``w`` [n, 4] weights, ``rot`` [n, 2, 2],
+    plus ``tangents`` = :func:`extended_tangents`.  Ghost cells between tiles of one face and the corner blocks (which
+    the stencil never reads) keep the plain copy: weight 1 on the copy's source, rot = the signed permutation.
+    """
+    from . import topology
+    if points < 2 or points > 4:
+        raise ValueError("points must be 2, 3 or 4")
+    tab = topology.build_halo_table(N, p, g) if table is None else table
+    n = N // p
+    m = n + 2 * g
+    pp = p * p
+    delta = 0.5 * np.pi / N
+    text = extended_tangents(N, g)
+    dst_face, src_face = tab["dst_tile"] // pp, tab["src_tile"] // pp
+    rd, rs = tab["dst_tile"] % pp, tab["src_tile"] % pp
+    # face-level indices (interior numbering, ghosts negative or >= N) of the ghost cell and of the copy's source
+    J = (rd // p) * n + tab["dst_j"] - g
+    I = (rd % p) * n + tab["dst_i"] - g
+    Js = (rs // p) * n + tab["src_j"] - g
+    Is = (rs % p) * n + tab["src_i"] - g
+    count = J.size
+    dst = (tab["dst_tile"] * m + tab["dst_j"]) * m + tab["dst_i"]
+    copy_src = (tab["src_tile"] * m + tab["src_j"]) * m + tab["src_i"]
+    src = np.repeat(copy_src[:, None], 4, axis=1)
+    w = np.zeros((count, 4))
+    w[:, 0] = 1.0
+    code = tab["code"]
+    rot = np.zeros((count, 2, 2))
+    swap = (code & 1) == 1
+    rot[~swap, 0, 0] = rot[~swap, 1, 1] = 1.0
+    rot[swap, 0, 1] = rot[swap, 1, 0] = 1.0
+    rot[(code & 2) != 0, 0, :] *= -1.0
+    rot[(code & 4) != 0, 1, :] *= -1.0
+    # seam edge strips: exactly one face-level index outside [0, N), and the source on another face
+    out_j, out_i = (J < 0) | (J >= N), (I < 0) | (I >= N)
+    sel = np.nonzero((out_j ^ out_i) & (dst_face != src_face))[0]
+    if sel.size:
+        L, B = dst_face[sel], src_face[sel]
+        fr = np.asarray(FACE_FRAMES, dtype=np.float64)
+        X, Y = text[I[sel] + g], text[J[sel] + g]
+        P = fr[L, 0] + X[:, None] * fr[L, 1] + Y[:, None] * fr[L, 2]
+        P /= np.linalg.norm(P, axis=-1, keepdims=True)
+        _, _, XB, YB = chart_basis(B, P, a)
+        fi = (np.arctan(XB) + 0.25 * np.pi) / delta - 0.5          # fractional interior indices in the neighbour
+        fj = (np.arctan(YB) + 0.25 * np.pi) / delta - 0.5
+        # the copy's source sits at the same depth: that index is the integer one, the other is interpolated along
+        along_j = np.abs(fi - Is[sel]) <= np.abs(fj - Js[sel])
+        depth_err = np.where(along_j, np.abs(fi - Is[sel]), np.abs(fj - Js[sel]))
+        if depth_err.max() > 1e-6:
+            raise RuntimeError("a ghost point does not lie on its neighbour's coordinate line (not an equiangular grid?)")
+        f = np.where(along_j, fj, fi)
+        b0 = np.clip(np.floor(f).astype(np.int64) - (points // 2 - 1), 0, N - points)
+        nodes = b0[:, None] + np.arange(4)[None, :]
+        nodes = np.minimum(nodes, (b0 + points - 1)[:, None])      # unused slots repeat the last node with weight 0
+        ws = np.zeros((sel.size, 4))
+        for q in range(points):
+            lag = np.ones(sel.size)
+            for r in range(points):
+                if r != q:
+                    lag *= (f - nodes[:, r]) / (nodes[:, q] - nodes[:, r])
+            ws[:, q] = lag
+        jb = np.where(along_j[:, None], nodes, Js[sel][:, None])
+        ib = np.where(along_j[:, None], Is[sel][:, None], nodes)
+        tile = B[:, None] * pp + (jb // n) * p + (ib // n)
+        src[sel] = (tile * m + jb % n + g) * m + ib % n + g
+        w[sel] = ws
+        rot[sel] = seam_rotation(L, B, XB, YB, "contravariant", a)
+    return {"dst": dst, "src": src, "w": w, "rot": rot, "tangents": text}
