@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-secondary", action="store_true", help="skip the fp64 side measurement")
     ap.add_argument("--new-state-sums", action="store_true",
                     help="per-step mass / energy of the NEW state (summed in the last stage) instead of the entry state (first stage)")
+    ap.add_argument("--halo-path", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: cross-GPU ghosts by one-sided peer stores (CUDA IPC over NVLink) or by pack / NCCL all-to-all / unpack")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the multi-GPU parity run that precedes the timing")
     return ap.parse_args()
 
@@ -337,7 +339,7 @@ def run_ours(args):
     # conservation sums every step, taken inside the first stage's launches (the state each step starts from)
     stepper = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
                                      advect_only=case.advect_only, device=local, rank=rank, world=world,
-                                     kernel=args.kernel, sums_of_entry_state=not args.new_state_sums)
+                                     kernel=args.kernel, sums_of_entry_state=not args.new_state_sums, halo_path=args.halo_path)
     assert (stepper.tile_begin, stepper.tile_count) == (t0, tc)
 
     def padded(field):
@@ -395,7 +397,7 @@ def run_ours(args):
     value = cells_total * args.steps / (ms * 1e-3)
     d_after = diag.cpu().numpy().tolist()
     finite = bool(torch.isfinite(dev[0]).all().item()) and bool(np.isfinite(d_after).all())
-    for _ in range(2):
+    for _ in range(4):                             # a new argument set: eager calls, then the graph capture, then a replay
         one_step(False)
     ms_nosums, _ = timed_steps(args.steps, with_sums=False)
 
@@ -461,6 +463,29 @@ def run_ours(args):
                 "what": "exchange_us = pack + NCCL all-to-all + unpack of one ghost fill, alone on an idle GPU, max over ranks; "
                         "exposed = step time minus the time of the same step with the cross-GPU exchange left out",
                 "path": stepper.halo_path}
+        if "peer stores" in stepper.halo_path and not args.no_secondary:
+            # the comparison arm: the same job with pack -> NCCL all-to-all -> unpack
+            alt = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
+                                         advect_only=case.advect_only, device=local, rank=rank, world=world,
+                                         kernel=args.kernel, sums_of_entry_state=not args.new_state_sums, halo_path="nccl")
+            adev = [x.clone() for x in dev]
+            alt.halo_fill(*adev)
+            for _ in range(5):
+                alt.step(*adev, dt, diag=diag)
+            barrier()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            for _ in range(args.steps):
+                alt.step(*adev, dt, diag=diag)
+            a1.record()
+            barrier()
+            t = torch.tensor([a0.elapsed_time(a1) / args.steps], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ah = alt.time_halo(adev, dt, reps=max(10, args.steps))
+            halo["nccl_arm"] = {"ms_per_step": float(t.item()), "exchange_us": ah["exchange_us"], "path": alt.halo_path}
+            alt.close()
+            del adev, alt
+            torch.cuda.empty_cache()
 
     # ---- end to end through the host-buffer entry point: a ROUND TRIP (state in, new state + sums out) --------
     e2e = None

@@ -14,7 +14,7 @@
  *     exception: the first cs_step for a new (h, u, v, dt, diag_out) combination captures and
  *     instantiates a CUDA graph (creates a stream, allocates graph memory; CS_STEP_GRAPH=0 opts out);
  *   - the set-up calls synchronise the device and/or allocate: cs_ctx_create, cs_ctx_destroy,
- *     cs_halo_set_rotation, cs_halo_set_interp, cs_halo_plan, and cs_step_host[_batch] (which own their copies);
+ *     cs_halo_set_rotation, cs_halo_set_interp, cs_halo_plan, cs_halo_peer_alloc, cs_halo_peer_connect, and cs_step_host[_batch] (which own their copies);
  *   - every call runs on the context's device and restores the calling thread's current CUDA
  *     device before it returns;
  *   - return value 0 = success, negative = CS_E_* below; the text of the last
@@ -264,6 +264,29 @@ CS_API int cs_halo_pack(cs_ctx* ctx, const void* h, const void* u, const void* v
                  void* sendbuf, void* stream);
 CS_API int cs_halo_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u, void* v, int nfields,
                    void* stream);
+
+/*
+ * The same exchange with one-sided peer stores over NVLink (GPUs of one box, one process per GPU) instead of
+ * pack -> all-to-all -> unpack.  Set-up, once, after cs_halo_plan:
+ *   cs_halo_peer_alloc   allocates this context's double-buffered receive buffer and flag words and writes their
+ *                        CUDA IPC handles (CS_PEER_HANDLE_BYTES bytes) to handles_out;
+ *   (the caller gathers every rank's handle block and receive counts, e.g. with torch.distributed.all_gather)
+ *   cs_halo_peer_connect maps the peers' buffers: all_handles = [n_peers][CS_PEER_HANDLE_BYTES] in rank order,
+ *                        remote_offsets[r] = the offset, in cells, of this rank's block inside rank r's receive
+ *                        buffer (the sum of r's receive counts from the ranks before this one).
+ * Per ghost fill, on every rank: cs_halo_push (gathers the boundary cells each peer needs and stores them straight
+ * into that peer's receive buffer, then raises the peer's flag for this rank) and cs_halo_pull (waits for the flags
+ * of this fill, scatters the buffer into the remote ghosts with the seam permutation).  Both only enqueue; fills
+ * are counted on the device, so the pair can be captured into a CUDA graph and replayed.  Every rank must issue
+ * the same sequence of fills; destroy the contexts only after all ranks have finished (the peers hold mappings).
+ * Replaces: the cross-device copies GSPMD inserts for .at[face].set(...) (PY:79,192-195); north_star names
+ * CUDA-IPC peer stores first, NCCL send/recv second.
+ */
+#define CS_PEER_HANDLE_BYTES 192
+CS_API int cs_halo_peer_alloc(cs_ctx* ctx, void* handles_out, size_t handles_bytes);
+CS_API int cs_halo_peer_connect(cs_ctx* ctx, int n_peers, int my_rank, const void* all_handles, const int64_t* remote_offsets);
+CS_API int cs_halo_push(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* stream);
+CS_API int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields, void* stream);
 
 /*
  * Split stage for overlap on shards: part = 0 computes cells that need no remote

@@ -217,6 +217,7 @@ extern "C" int cs_ctx_destroy(cs_ctx* ctx) {
     if (!ctx) return CS_OK;
     CsDeviceGuard guard(ctx->device);
     cudaDeviceSynchronize();
+    cs_peer_destroy(ctx);
     cs_drop_graphs(ctx);
     if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
     for (cudaStream_t s : {ctx->pipe.in, ctx->pipe.compute, ctx->pipe.out})

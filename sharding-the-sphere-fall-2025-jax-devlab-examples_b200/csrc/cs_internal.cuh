@@ -51,8 +51,12 @@ struct CsTuning {
     int fused_diag = 1;          // CS_FUSED_DIAG: 0 = diagnostics of a step by the separate reduction kernel
 };
 
+struct cs_peer_state;   // one-sided exchange over CUDA IPC mappings (cs_peer.cu)
+void cs_peer_destroy(struct cs_ctx* ctx);
+
 struct cs_ctx {
     cs_config cfg;
+    cs_peer_state* peer = nullptr;
     CsTuning tune;
     int N = 0, p = 0, n = 0, g = 0, m = 0;
     int T_all = 0, t0 = 0, T = 0;

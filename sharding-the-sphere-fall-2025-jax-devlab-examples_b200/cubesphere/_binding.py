@@ -16,6 +16,7 @@ CS_ABI_VERSION = 1
 CS_OK, CS_E_INVALID, CS_E_UNSUPPORTED, CS_E_CUDA, CS_E_NOMEM = 0, -1, -2, -3, -4
 CS_F32, CS_F64 = 0, 1
 CS_SUMS_OF_OUTPUT, CS_SUMS_OF_INPUT = 0, 1
+CS_PEER_HANDLE_BYTES = 192
 RK_IDS = {"euler": 1, "ssprk2": 2, "ssprk3": 3}
 LIMITER_IDS = {"none": 0, "minmod": 1, "mc": 2}
 KERNEL_IDS = {"auto": 0, "naive": 1, "march": 2, "tma": 3}
@@ -60,6 +61,10 @@ _PROTOTYPES = {
                                C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "cs_halo_pack": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP, _VP]),
     "cs_halo_unpack": (C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
+    "cs_halo_peer_alloc": (C.c_int, [_VP, _VP, C.c_size_t]),
+    "cs_halo_peer_connect": (C.c_int, [_VP, C.c_int, C.c_int, _VP, C.POINTER(C.c_int64)]),
+    "cs_halo_push": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP]),
+    "cs_halo_pull": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_launch_count": (C.c_int64, [_VP]),
     "cs_step_kernel_trace": (C.c_int, [_VP, C.c_int, C.POINTER(C.c_uint64)]),
     "cs_stage_kernel_info": (C.c_int, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),

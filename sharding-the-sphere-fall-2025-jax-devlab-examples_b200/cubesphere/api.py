@@ -457,6 +457,31 @@ class Context:
         self._check(self._lib.cs_halo_unpack(self._h, C.c_void_p(recvbuf.data_ptr()), self._ptr(h, "h"), up, vp,
                                              nfields, self._stream()))
 
+    # one-sided exchange over CUDA IPC (GPUs of one box)
+    def halo_peer_alloc(self):
+        """This context's IPC handle block (bytes) for its receive buffers and flags; gather all ranks' blocks."""
+        buf = C.create_string_buffer(B.CS_PEER_HANDLE_BYTES)
+        self._check(self._lib.cs_halo_peer_alloc(self._h, buf, B.CS_PEER_HANDLE_BYTES))
+        return buf.raw
+
+    def halo_peer_connect(self, my_rank, all_handles, remote_offsets):
+        blob = b"".join(all_handles)
+        n = len(all_handles)
+        if len(blob) != n * B.CS_PEER_HANDLE_BYTES or len(remote_offsets) != n:
+            raise ValueError("need one handle block and one offset per rank")
+        off = (C.c_int64 * n)(*[int(x) for x in remote_offsets])
+        self._check(self._lib.cs_halo_peer_connect(self._h, n, int(my_rank), C.c_char_p(blob), off))
+
+    def halo_push(self, h, u, v, nfields=3):
+        up = self._ptr(u, "u") if u is not None else None
+        vp = self._ptr(v, "v") if v is not None else None
+        self._check(self._lib.cs_halo_push(self._h, self._ptr(h, "h"), up, vp, nfields, self._stream()))
+
+    def halo_pull(self, h, u, v, nfields=3):
+        up = self._ptr(u, "u") if u is not None else None
+        vp = self._ptr(v, "v") if v is not None else None
+        self._check(self._lib.cs_halo_pull(self._h, self._ptr(h, "h"), up, vp, nfields, self._stream()))
+
 
 # ----------------------------------------------------------------------------
 # the reference's factories

@@ -33,7 +33,7 @@ RK_PAIRS = {
 class ShardedStepper:
     def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f32", rk="ssprk3", limiter="mc", advect_only=False,
                  axis=(0.0, 0.0, 1.0), device=0, rank=0, world=1, kernel="auto", tangents=None, overlap=True,
-                 group=None, use_graph=True, sums_of_entry_state=False):
+                 group=None, use_graph=True, sums_of_entry_state=False, halo_path="peer"):
         # sums_of_entry_state: step(..., diag) reports mass / energy of the state the step STARTS from, summed inside
         # the first stage's launches (a few instructions per cell); default: of the new state, inside the last stage's
         self.sums_of_entry_state = bool(sums_of_entry_state)
@@ -64,7 +64,17 @@ class ShardedStepper:
             self.qb = [self.ctx.new_field() for _ in range(3)]
             self._diag = torch.zeros(2, dtype=torch.float64, device=dev)
             self._sums4 = torch.zeros(4, dtype=torch.float64, device=dev)    # [inner mass, energy, rim mass, energy]
-        self.halo_path = "single device: one ghost-fill launch" if world == 1 else "pack -> NCCL all_to_all_single -> unpack"
+        self.halo_path = "single device: one ghost-fill launch"
+        if world > 1:
+            # cross-GPU ghosts: one-sided peer stores over NVLink (CUDA IPC mappings, one push and one pull kernel per
+            # fill) or, as the comparison arm and the fallback, pack -> NCCL all-to-all -> unpack
+            if halo_path not in ("peer", "nccl"):
+                raise ValueError(f"halo_path must be 'peer' or 'nccl', got {halo_path!r}")
+            self._peer = False
+            if halo_path == "peer":
+                self._peer = self._connect_peers()
+            self.halo_path = ("peer stores into the neighbours' receive buffers (CUDA IPC over NVLink) + flag, then pull"
+                              if self._peer else "pack -> NCCL all_to_all_single -> unpack")
 
     # -- bookkeeping ------------------------------------------------------------------------
     @property
@@ -75,12 +85,39 @@ class ShardedStepper:
         # graphs hold NCCL work: drop them (and drain the device) before the process group goes away
         self._graphs.clear()
         torch.cuda.synchronize(self.device)
+        if self.world > 1 and getattr(self, "_peer", False) and dist.is_initialized():
+            dist.barrier(group=self.group)                 # peers hold mappings of this context's buffers
         self.ctx.close()
+
+    def _connect_peers(self):
+        """Exchange IPC handles and receive counts, map the peers' buffers.  False (-> NCCL path) when a rank cannot."""
+        ok, handle = 1, b""
+        try:
+            handle = self.ctx.halo_peer_alloc()
+        except Exception:
+            ok = 0
+        everyone = [None] * self.world
+        dist.all_gather_object(everyone, (ok, handle, list(self.recv_counts)), group=self.group)
+        if not all(e[0] for e in everyone):
+            return False
+        # my block inside rank r's receive buffer starts after the blocks of the ranks before me
+        remote = [sum(everyone[r][2][:self.rank]) for r in range(self.world)]
+        try:
+            self.ctx.halo_peer_connect(self.rank, [e[1] for e in everyone], remote)
+        except Exception:
+            ok = 0
+        flags = [None] * self.world
+        dist.all_gather_object(flags, ok, group=self.group)
+        return all(flags)
 
     # -- halo -------------------------------------------------------------------------------
     def _exchange(self, h, u, v, nfields=3):
         """pack -> all-to-all -> unpack on the current stream (remote ghosts only)."""
         if self._skip_exchange:
+            return
+        if self._peer:
+            self.ctx.halo_push(h, u, v, nfields)
+            self.ctx.halo_pull(h, u, v, nfields)
             return
         self.ctx.halo_pack(h, u, v, self.sendbuf, nfields)
         ns = nfields * sum(self.send_counts)
@@ -142,6 +179,7 @@ class ShardedStepper:
         pairs = RK_PAIRS[self.rk]
         main = torch.cuda.current_stream(self.device)
         ev_rim = ev_inner = None
+        pending_sums = False
         for k, (a, b) in enumerate(pairs):
             last = k == len(pairs) - 1 and len(pairs) > 1
             out = q0 if last else (self.qa if k % 2 == 0 else self.qb)
@@ -159,6 +197,11 @@ class ShardedStepper:
                         self.comm_stream.wait_stream(main)                     # whatever came before the step
                     else:
                         self.comm_stream.wait_event(ev_inner)                  # rim reads inner cells next to it
+                        if pending_sums:
+                            # entry-state sums came out of stage 1 (inner + rim kernels, both finished by now):
+                            # combine them across ranks here, on the side stream, under the cover of stage 2
+                            self._combine_sums(diag)
+                            pending_sums = False
                     self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1, diag=self._sums4[2:] if sums else None, sums_of_input=sin)
                     ev_rim_new = torch.cuda.Event()
                     ev_rim_new.record(self.comm_stream)
@@ -170,6 +213,7 @@ class ShardedStepper:
                 ev_inner = torch.cuda.Event()
                 ev_inner.record(main)
                 ev_rim = ev_rim_new
+                pending_sums = pending_sums or (sums and sin and k < len(pairs) - 1)
             else:
                 if sums:
                     self._sums4[2:].zero_()
@@ -179,14 +223,17 @@ class ShardedStepper:
             cur = out
         if self.overlap:
             main.wait_stream(self.comm_stream)
-        if diag is not None:
-            # rank-local (inner, rim) sums -> whole sphere: one all-reduce of four doubles, then inner + rim
-            dist.all_reduce(self._sums4, group=self.group)
-            torch.add(self._sums4[:2], self._sums4[2:], out=diag)
+        if diag is not None and not (self.overlap and self.sums_of_entry_state and len(pairs) > 1):
+            self._combine_sums(diag)                       # sums of the new state: only now are they complete
         if len(pairs) == 1:
             for x, y in zip(q0, cur):
                 x.copy_(y)
         return h, u, v
+
+    def _combine_sums(self, diag):
+        """Rank-local (inner, rim) sums -> whole sphere: one all-reduce of four doubles, then inner + rim."""
+        dist.all_reduce(self._sums4, group=self.group)
+        torch.add(self._sums4[:2], self._sums4[2:], out=diag)
 
     def diagnostics(self, h, u, v):
         """[mass, energy] of the whole sphere on every rank (fp64)."""

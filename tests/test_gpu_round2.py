@@ -213,22 +213,27 @@ def test_auto_fallback_to_the_slow_kernel_is_visible(built_library):
 def test_entry_points_restore_the_callers_device(built_library):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two visible GPUs")
-    rt = torch.cuda.cudart()
-    rt.cudaSetDevice(1)
+    case, par, ref, ctx, dev = _setup("tc2", 24, 1, np.float64)       # context and state on cuda:0
+    torch.cuda.synchronize(0)
+    torch.cuda.set_device(1)                                           # the caller's thread works on another device
     try:
-        case, par, ref, ctx, dev = _setup("tc2", 24, 1, np.float64)   # context and state on cuda:0
-        assert torch.cuda.current_device() == 1
         null = C.c_void_p(None)
         lib = built_library
         rc = lib.cs_halo_fill_state(ctx._h, *(C.c_void_p(x.data_ptr()) for x in dev), null)
         assert rc == 0 and torch.cuda.current_device() == 1
         rc = lib.cs_step(ctx._h, *(C.c_void_p(x.data_ptr()) for x in dev), cases.stable_dt(case, 0.5), null, null)
         assert rc == 0 and torch.cuda.current_device() == 1
+        # a context created and destroyed for device 0 while device 1 is current
+        other = api.Context(24, halo=2, dtype=np.float64, device=0)
+        assert torch.cuda.current_device() == 1
+        other.close()
         ctx.close()
         assert torch.cuda.current_device() == 1
     finally:
-        rt.cudaSetDevice(0)
+        torch.cuda.set_device(0)
     torch.cuda.synchronize(0)
+    ref = orc.step(par, ref, cases.stable_dt(case, 0.5))
+    assert np.allclose(dev[0].cpu().numpy()[:, 2:26, 2:26], ref[0][:, 2:26, 2:26], rtol=1e-13, atol=0)
 
 
 # ---------------------------------------------------------------------------------------------------------------

@@ -105,9 +105,8 @@ def test_callers_current_device_is_left_alone(built_library):
     lib = built_library
     g, N = 2, 24
     case, dev, _ = _state("tc2", N, 1, g, torch.float64)          # state on cuda:0
-    rt = torch.cuda.cudart()
     torch.cuda.synchronize(0)
-    rt.cudaSetDevice(1)
+    torch.cuda.set_device(1)
     try:
         out = torch.zeros(2, dtype=torch.float64, device="cuda:0")
         rc = lib.cs_diagnostics_noalloc(B.CS_F64, N, 1, g, 0, 0, 0.0, 0.0, C.c_void_p(dev[0].data_ptr()),
@@ -116,7 +115,7 @@ def test_callers_current_device_is_left_alone(built_library):
         assert rc == B.CS_OK
         assert torch.cuda.current_device() == 1
     finally:
-        rt.cudaSetDevice(0)
+        torch.cuda.set_device(0)
     torch.cuda.synchronize(0)
     ref = _oracle_diag(case, N, g, torch.float64)
     assert np.all(np.abs(out.cpu().numpy() - ref) <= 1e-12 * np.abs(ref))

@@ -18,7 +18,8 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ok = True
-for N, p, overlap, entry in ((48, 2 if world > 3 else 1, True, False), (96, 2, True, True), (96, 2, False, False)):
+for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "peer"), (96, 2, True, True, "peer"),
+                                   (96, 2, True, False, "nccl"), (96, 2, False, False, "peer"), (96, 2, False, True, "nccl")):
     if (6 * p * p) % world:
         continue
     g, steps = 2, 10
@@ -26,7 +27,10 @@ for N, p, overlap, entry in ((48, 2 if world > 3 else 1, True, False), (96, 2, T
     par = orc.Params(N, g, axis=case.axis, hs=case.hs)
     ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
     st = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis, device=local, rank=rank,
-                                world=world, tangents=orc.centre_tangents(N), overlap=overlap, sums_of_entry_state=entry)
+                                world=world, tangents=orc.centre_tangents(N), overlap=overlap, sums_of_entry_state=entry, halo_path=path)
+    if path == "peer" and "peer stores" not in st.halo_path:
+        print(f"rank {rank}: the peer path fell back to NCCL ({st.halo_path})", flush=True)
+        ok = False
     b, c = st.tile_begin, st.tile_count
     n = N // p
     raw = [orc.faces_to_tiles(orc.pad(x, g), p, g)[b:b + c] for x in (case.h, case.u1, case.u2)]   # ghosts empty
@@ -54,7 +58,7 @@ for N, p, overlap, entry in ((48, 2 if world > 3 else 1, True, False), (96, 2, T
     good = max(errs) <= 1e-12 and abs(m1[0] - m0[0]) <= 1e-13 * m0[0] and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
     good = good and abs(mf[0] - mfo[0]) <= 1e-13 * mfo[0] and abs(mf[1] - mfo[1]) <= 1e-12 * abs(mfo[1])
     ok = ok and good
-    print(f"rank {rank}/{world} C{N} p={p} overlap={overlap} entry_sums={entry}: max rel err {max(errs):.2e}, mass drift {(m1[0]-m0[0])/m0[0]:.1e} -> {'ok' if good else 'FAIL'}", flush=True)
+    print(f"rank {rank}/{world} C{N} p={p} overlap={overlap} entry_sums={entry} halo={path}: max rel err {max(errs):.2e}, mass drift {(m1[0]-m0[0])/m0[0]:.1e} -> {'ok' if good else 'FAIL'}", flush=True)
     st.close()
 t = torch.tensor([int(ok)], device="cuda")
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
