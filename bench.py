@@ -460,7 +460,7 @@ def run_ours(args):
                 "halo_us_per_step": h["exchange_us"] * len(roof["ms"]),
                 "step_ms_without_exchange": h["step_ms_without_exchange"],
                 "exposed_us_per_step": (ms_nosums / args.steps - h["step_ms_without_exchange"]) * 1e3,
-                "what": "exchange_us = pack + NCCL all-to-all + unpack of one ghost fill, alone on an idle GPU, max over ranks; "
+                "what": "exchange_us = the cross-GPU part of one ghost fill (push + pull, or pack + all-to-all + unpack), alone on an idle GPU, max over ranks; "
                         "exposed = step time minus the time of the same step with the cross-GPU exchange left out",
                 "path": stepper.halo_path}
         if "peer stores" in stepper.halo_path and not args.no_secondary:

@@ -216,6 +216,17 @@ CS_API int cs_rk_stage(cs_ctx* ctx, const void* const q0[3], const void* const q
 CS_API int cs_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag_out, void* stream);
 
 /*
+ * Demo workload (deck slides 12, 17: heat diffusing from a checkerboard source on the top panel, "proof that
+ * sharding works"): one explicit step of scalar diffusion, Tout = T + kappa_dt * L(T) + dt_source * source on the
+ * interior cells, L = the 5-point flux-form Laplacian with the panel metric (no cross-derivative terms: those need
+ * the corner ghosts no panel owns), then Tout's ghosts are filled.  T must be ghost-filled; source may be NULL; same
+ * layout and dtype as the state.  Total heat sum sqrt(G) T is conserved to round-off (single-valued seam fluxes).
+ * Stable for kappa_dt <= delta^2 / (4 max g^ii).  Replaces: the thermal-diffusion demo solver (not shipped upstream).
+ */
+CS_API int cs_scalar_diffuse(cs_ctx* ctx, const void* T, void* Tout, const void* source, double kappa_dt, double dt_source,
+                      void* stream);
+
+/*
  * Mass  M = sum sqrt(G) h dalpha dbeta  and total energy
  * E = sum sqrt(G) (h K + g h^2 / 2 + g h hs) dalpha dbeta  over the owned interior
  * cells, accumulated in fp64 in a fixed order (deterministic); out = device

@@ -363,3 +363,33 @@ def tiles_to_faces(tiles, p, g):
                 out[f, g + ty * n:g + ty * n + n, g + tx * n:g + tx * n + n] = \
                     tiles[f * p * p + ty * p + tx, g:g + n, g:g + n]
     return out
+
+
+# ----------------------------------------------------------------------------
+# demo workload: scalar diffusion (the reference's heat-diffusion "proof that sharding works", deck slides 12, 17)
+# ----------------------------------------------------------------------------
+
+def diffuse(p: Params, T, kappa_dt, source=None, dt_source=0.0):
+    """One explicit step of the 5-point flux-form diffusion of a ghost-filled scalar ``T [6, M, M]``:
+    T + kappa_dt / (sqrt(G) delta^2) [d_a(W1 d_a T) + d_b(W2 d_b T)] + dt_source * source, W1 = sqrt(G) g^11 and
+    W2 = sqrt(G) g^22 averaged to the faces (no cross-derivative terms; see csrc/cs_scalar.cu).  Ghosts refilled."""
+    g, N = p.g, p.N
+    c = slice(g, g + N)
+    w1, w2 = p.sg * p.gi11, p.sg * p.gi22
+    FE = 0.5 * (w1[c, g:g + N] + w1[c, g + 1:g + N + 1]) * (T[:, c, g + 1:g + N + 1] - T[:, c, c])
+    FW = 0.5 * (w1[c, g - 1:g + N - 1] + w1[c, g:g + N]) * (T[:, c, c] - T[:, c, g - 1:g + N - 1])
+    GN = 0.5 * (w2[g:g + N, c] + w2[g + 1:g + N + 1, c]) * (T[:, g + 1:g + N + 1, c] - T[:, c, c])
+    GS = 0.5 * (w2[g - 1:g + N - 1, c] + w2[g:g + N, c]) * (T[:, c, c] - T[:, g - 1:g + N - 1, c])
+    out = np.zeros_like(T)
+    out[:, c, c] = T[:, c, c] + (kappa_dt / (p.delta * p.delta)) * (((FE - FW) + (GN - GS)) / p.sg[c, c])
+    if source is not None:
+        out[:, c, c] += dt_source * source[:, c, c]
+    return halo_fill_scalar(out, g)
+
+
+def checkerboard_source(N, g, squares=4, amplitude=1.0):
+    """The demo's heat source: a checkerboard of ``squares`` x ``squares`` patches on the top panel (face 0)."""
+    src = np.zeros((6, N + 2 * g, N + 2 * g))
+    k = (np.arange(N) * squares) // N
+    src[0, g:g + N, g:g + N] = amplitude * (((k[:, None] + k[None, :]) % 2) == 0)
+    return src

@@ -401,6 +401,14 @@ class Context:
                                              C.c_void_p(out.data_ptr()), self._stream()))
         return out
 
+    def scalar_diffuse(self, T, Tout, kappa_dt, source=None, dt_source=0.0):
+        """One explicit diffusion step of a scalar tracer (the reference's heat-diffusion demo): ``Tout`` gets
+        ``T + kappa_dt L(T) + dt_source source`` and filled ghosts.  ``T`` must be ghost-filled."""
+        sp = self._ptr(source, "source") if source is not None else None
+        self._check(self._lib.cs_scalar_diffuse(self._h, self._ptr(T, "T"), self._ptr(Tout, "Tout"), sp, float(kappa_dt),
+                                                float(dt_source), self._stream()))
+        return Tout
+
     def _host_ptrs(self, h, u, v):
         ptrs = []
         np_dtype = np.float64 if self.dtype is torch.float64 else np.float32

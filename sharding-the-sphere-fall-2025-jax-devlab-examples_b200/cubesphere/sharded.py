@@ -60,6 +60,7 @@ class ShardedStepper:
             self.sendbuf = torch.zeros(max(1, 3 * sum(self.send_counts)), dtype=self.ctx.dtype, device=dev)
             self.recvbuf = torch.zeros(max(1, 3 * sum(self.recv_counts)), dtype=self.ctx.dtype, device=dev)
             self.comm_stream = torch.cuda.Stream(device=device)
+            self.sums_stream = torch.cuda.Stream(device=device)
             self.qa = [self.ctx.new_field() for _ in range(3)]
             self.qb = [self.ctx.new_field() for _ in range(3)]
             self._diag = torch.zeros(2, dtype=torch.float64, device=dev)
@@ -179,7 +180,7 @@ class ShardedStepper:
         pairs = RK_PAIRS[self.rk]
         main = torch.cuda.current_stream(self.device)
         ev_rim = ev_inner = None
-        pending_sums = False
+        pending_sums = joined_sums = False
         for k, (a, b) in enumerate(pairs):
             last = k == len(pairs) - 1 and len(pairs) > 1
             out = q0 if last else (self.qa if k % 2 == 0 else self.qb)
@@ -198,10 +199,14 @@ class ShardedStepper:
                     else:
                         self.comm_stream.wait_event(ev_inner)                  # rim reads inner cells next to it
                         if pending_sums:
-                            # entry-state sums came out of stage 1 (inner + rim kernels, both finished by now):
-                            # combine them across ranks here, on the side stream, under the cover of stage 2
-                            self._combine_sums(diag)
+                            # entry-state sums came out of stage 1 (inner + rim kernels, both finished by now): combine
+                            # them across ranks on a stream of their own, under the cover of stages 2 and 3 -- not on
+                            # this one, where the all-reduce would hold up the rim and the exchange behind it
+                            self.sums_stream.wait_stream(self.comm_stream)
+                            with torch.cuda.stream(self.sums_stream):
+                                self._combine_sums(diag)
                             pending_sums = False
+                            joined_sums = True
                     self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1, diag=self._sums4[2:] if sums else None, sums_of_input=sin)
                     ev_rim_new = torch.cuda.Event()
                     ev_rim_new.record(self.comm_stream)
@@ -223,6 +228,8 @@ class ShardedStepper:
             cur = out
         if self.overlap:
             main.wait_stream(self.comm_stream)
+            if joined_sums:
+                main.wait_stream(self.sums_stream)
         if diag is not None and not (self.overlap and self.sums_of_entry_state and len(pairs) > 1):
             self._combine_sums(diag)                       # sums of the new state: only now are they complete
         if len(pairs) == 1:

@@ -450,3 +450,41 @@ def test_interpolated_halo_is_second_order_on_the_gpu(built_library):
     order = {m: np.log2(errs[m, 24] / errs[m, 48]) for m in ("copy", "interp")}
     print("orders", order, errs)
     assert order["interp"] > 1.8 and order["copy"] < 1.5 and errs["interp", 48] < 0.2 * errs["copy", 48]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# f3: the reference's heat-diffusion demo on the scalar ghost fill
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("N,p,dtype,tol", [(24, 1, np.float64, 1e-13), (32, 2, np.float64, 1e-13), (32, 1, np.float32, 5e-6)])
+def test_diffusion_demo_matches_the_oracle(built_library, N, p, dtype, tol):
+    """Checkerboard heat source on the top panel (deck slide 12), 100 explicit diffusion steps through
+    cs_scalar_diffuse, against the oracle; four equal shares on the four neighbouring panels; heat conserved once the
+    source is switched off."""
+    g = 2
+    par = orc.Params(N, g)
+    src = orc.checkerboard_source(N, g)
+    c = slice(g, g + N)
+    kdt = 0.2 * par.delta ** 2 / max(par.gi11[c, c].max(), par.gi22[c, c].max())
+    ctx = api.Context(N, tiles_per_edge=p, halo=g, dtype=dtype, tangents=orc.centre_tangents(N))
+    a, b = ctx.new_field(), ctx.new_field()
+    dsrc = torch.from_numpy(orc.faces_to_tiles(src, p, g).astype(dtype)).cuda()
+    ref = np.zeros_like(src)
+    for _ in range(100):
+        ctx.scalar_diffuse(a, b, kdt, source=dsrc, dt_source=1.0)
+        a, b = b, a
+        ref = orc.diffuse(par, ref, kdt, src, 1.0)
+    got = orc.tiles_to_faces(a.cpu().numpy().astype(np.float64), p, g)
+    assert np.linalg.norm(got - ref) <= tol * np.linalg.norm(ref)          # ghosts included
+    heat = lambda A: np.sum(par.sg[c, c] * A[:, c, c], axis=(1, 2))
+    shares = heat(got)[1:5]
+    assert np.ptp(shares) <= (1e-12 if dtype is np.float64 else 1e-5) * shares.mean()
+    total0 = heat(got).sum()
+    for _ in range(100):
+        ctx.scalar_diffuse(a, b, kdt)
+        a, b = b, a
+    got = orc.tiles_to_faces(a.cpu().numpy().astype(np.float64), p, g)
+    assert abs(heat(got).sum() - total0) <= (1e-13 if dtype is np.float64 else 1e-6) * total0
+    with pytest.raises(ValueError):
+        ctx.scalar_diffuse(a, a, kdt)
+    ctx.close()

@@ -204,3 +204,27 @@ def test_seam_study_interpolated_ghosts_are_second_order():
     c32, dc32, _ = seam_study.run_case(32, "copy", 0.25)
     assert e32 < 0.2 * c32                                  # an order of magnitude more accurate at C32 already
     assert abs(dc32) < 1e-14 and 1e-9 < abs(d32) < 1e-4     # round-off vs truncation-level mass drift
+
+
+def test_diffusion_demo_conserves_heat_and_spreads_over_the_seams():
+    """The reference's visual demo as numbers: heat injected as a checkerboard on the top panel diffuses onto the four
+    neighbouring panels in equal shares (the pattern is symmetric under quarter turns of face 0, and so must be what
+    crosses its four seams), and without a source the total heat sum sqrt(G) T stays put to round-off."""
+    N, g = 24, 2
+    p = orc.Params(N, g)
+    src = orc.checkerboard_source(N, g)
+    c = slice(g, g + N)
+    kdt = 0.2 * p.delta ** 2 / max(p.gi11[c, c].max(), p.gi22[c, c].max())
+    T = np.zeros((6, N + 2 * g, N + 2 * g))
+    for _ in range(200):
+        T = orc.diffuse(p, T, kdt, src, 1.0)
+    heat = lambda A: np.sum(p.sg[c, c] * A[:, c, c], axis=(1, 2))
+    per_face = heat(T)
+    ring = per_face[1:5]
+    assert ring.min() > 0 and np.ptp(ring) <= 1e-12 * ring.mean()          # four seams, four equal shares
+    assert per_face[5] < 1e-3 * ring.mean()                                # the far panel is still cold
+    total0 = per_face.sum()
+    for _ in range(200):
+        T = orc.diffuse(p, T, kdt)
+    assert abs(heat(T).sum() - total0) <= 1e-13 * total0
+    assert heat(T)[1:5].min() > ring.max()                                 # and it keeps spreading outwards
