@@ -65,6 +65,11 @@ class ShardedStepper:
             self.qb = [self.ctx.new_field() for _ in range(3)]
             self._diag = torch.zeros(2, dtype=torch.float64, device=dev)
             self._sums4 = torch.zeros(4, dtype=torch.float64, device=dev)    # [inner mass, energy, rim mass, energy]
+            # deferred mode (diag="history"): every step's rank-local sums are appended here on the device and ONE
+            # all-reduce combines the whole record when it is read (read_sums)
+            self.history_capacity = 4096
+            self._hist = torch.zeros(self.history_capacity, 4, dtype=torch.float64, device=dev)
+            self._hist_idx = torch.zeros(1, dtype=torch.int64, device=dev)
         self.halo_path = "single device: one ghost-fill launch"
         if world > 1:
             # cross-GPU ghosts: one-sided peer stores over NVLink (CUDA IPC mappings, one push and one pull kernel per
@@ -145,15 +150,22 @@ class ShardedStepper:
 
     # -- step -------------------------------------------------------------------------------
     def step(self, h, u, v, dt, diag=None):
-        """One time step in place.  ``diag`` (device fp64 tensor [2], optional) receives mass and total energy of the
-        new state, whole sphere: the sums come out of the last stage's launches (no extra pass over the state), and
-        across ranks they are combined by one all-reduce of four doubles."""
+        """One time step in place.  ``diag`` (device fp64 tensor [2], optional) receives mass and total energy, whole
+        sphere: the sums come out of a stage's launches (no extra pass over the state), and across ranks they are
+        combined by one all-reduce of four doubles per step.  ``diag="history"`` (world > 1) defers the collective:
+        the rank-local sums of every step are appended to an on-device record and :meth:`read_sums` combines the whole
+        record in one all-reduce."""
+        if isinstance(diag, str) and diag != "history":
+            raise ValueError("diag must be a device tensor, None or 'history'")
         if self.world == 1:
+            if isinstance(diag, str):
+                raise ValueError("diag='history' is the multi-GPU deferred mode; pass a tensor on one GPU")
             self.ctx.step(h, u, v, dt, diag=diag)
             return h, u, v
         if not self.use_graph:
             return self._step_sharded(h, u, v, dt, diag)
-        key = (float(dt), h.data_ptr(), u.data_ptr(), v.data_ptr(), diag.data_ptr() if diag is not None else 0)
+        key = (float(dt), h.data_ptr(), u.data_ptr(), v.data_ptr(),
+               0 if diag is None else -1 if isinstance(diag, str) else diag.data_ptr())
         graph = self._graphs.get(key)
         if graph is None:
             # the first two calls run eagerly (NCCL warm-up, lazy initialisation), the third is captured
@@ -238,9 +250,26 @@ class ShardedStepper:
         return h, u, v
 
     def _combine_sums(self, diag):
-        """Rank-local (inner, rim) sums -> whole sphere: one all-reduce of four doubles, then inner + rim."""
+        """Rank-local (inner, rim) sums -> whole sphere: one all-reduce of four doubles, then inner + rim.
+        ``diag == "history"``: no collective now -- append the local sums to the on-device record instead."""
+        if isinstance(diag, str):
+            self._hist.index_copy_(0, self._hist_idx, self._sums4.unsqueeze(0))
+            self._hist_idx.add_(1)
+            return
         dist.all_reduce(self._sums4, group=self.group)
         torch.add(self._sums4[:2], self._sums4[2:], out=diag)
+
+    def read_sums(self):
+        """Deferred mode: [steps, 2] (mass, energy) of the whole sphere for every step taken with ``diag="history"``
+        since the last call -- one all-reduce for the whole record -- and the record starts again."""
+        n = int(self._hist_idx.item())
+        if n > self.history_capacity:
+            raise RuntimeError(f"{n} steps recorded, the history holds {self.history_capacity}: read it more often")
+        rec = self._hist[:n].clone()
+        if self.world > 1:
+            dist.all_reduce(rec, group=self.group)
+        self._hist_idx.zero_()
+        return rec[:, :2] + rec[:, 2:]
 
     def diagnostics(self, h, u, v):
         """[mass, energy] of the whole sphere on every rank (fp64)."""

@@ -57,6 +57,17 @@ for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "pee
     mfo = mo_entry if entry else mo                    # entry mode: the fused sums are those of the state before the last step
     good = max(errs) <= 1e-12 and abs(m1[0] - m0[0]) <= 1e-13 * m0[0] and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
     good = good and abs(mf[0] - mfo[0]) <= 1e-13 * mfo[0] and abs(mf[1] - mfo[1]) <= 1e-12 * abs(mfo[1])
+    # deferred sums: three more steps recorded on the device, one all-reduce when read
+    rec_ref = []
+    for _ in range(3):
+        rec_ref.append(orc.diagnostics(par, *ref))
+        st.step(*dev, dt, diag="history")
+        ref = orc.step(par, ref, dt)
+    if not entry:
+        rec_ref = rec_ref[1:] + [orc.diagnostics(par, *ref)]
+    rec = st.read_sums().cpu().numpy()
+    good = good and rec.shape == (3, 2) and all(abs(rec[k, 0] - rec_ref[k][0]) <= 1e-13 * rec_ref[k][0] and
+                                                abs(rec[k, 1] - rec_ref[k][1]) <= 1e-12 * abs(rec_ref[k][1]) for k in range(3))
     ok = ok and good
     print(f"rank {rank}/{world} C{N} p={p} overlap={overlap} entry_sums={entry} halo={path}: max rel err {max(errs):.2e}, mass drift {(m1[0]-m0[0])/m0[0]:.1e} -> {'ok' if good else 'FAIL'}", flush=True)
     st.close()
