@@ -342,6 +342,14 @@ CS_API int cs_diagnostics_noalloc(int dtype, int N, int tiles_per_edge, int halo
                                   const void* hs, double* out, int device, void* stream);
 
 /*
+ * Tuning knobs of one context, by name (the CS_* environment variables of DESIGN.md section 4 set the same knobs
+ * for every context at creation): "march_prefetch", "march_rows", "march_vec", "march_unit", "reserve_sms",
+ * "tma_ring", "fused_halo", "step_graph", "fused_diag", "step_kernel".  Drops the context's captured step graphs.
+ * Replaces: nothing (tuning).
+ */
+CS_API int cs_ctx_set_option(cs_ctx* ctx, const char* name, int value);
+
+/*
  * Which stage kernel ran: *last_variant = CS_KERNEL_* of the most recent cs_rk_stage / cs_step launch
  * (CS_KERNEL_AUTO before the first one), *naive_fallbacks = how many launches a CS_KERNEL_AUTO context had to
  * send to the one-thread-per-cell kernel (about 4x slower) because the fields were not 16-byte aligned, the row

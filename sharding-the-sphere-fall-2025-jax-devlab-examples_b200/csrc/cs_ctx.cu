@@ -34,6 +34,23 @@ extern "C" const char* cs_last_error(const cs_ctx* ctx) { return ctx ? ctx->err.
 
 extern "C" int64_t cs_launch_count(const cs_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
+extern "C" int cs_ctx_set_option(cs_ctx* ctx, const char* name, int value) {
+    if (!ctx || !name) return cs_fail(ctx, CS_E_INVALID, "cs_ctx_set_option: NULL argument");
+    struct { const char* key; int* slot; } opts[] = {
+        {"march_prefetch", &ctx->tune.march_prefetch}, {"march_rows", &ctx->tune.march_rows}, {"march_vec", &ctx->tune.march_vec},
+        {"march_unit", &ctx->tune.march_unit},         {"reserve_sms", &ctx->tune.reserve_sms}, {"tma_ring", &ctx->tune.tma_ring},
+        {"fused_halo", &ctx->tune.fused_halo},         {"step_graph", &ctx->tune.step_graph},   {"fused_diag", &ctx->tune.fused_diag},
+        {"step_kernel", &ctx->tune.step_kernel},
+    };
+    for (auto& o : opts)
+        if (std::strcmp(o.key, name) == 0) {
+            *o.slot = value;
+            cs_drop_graphs(ctx);                          // captured steps have the old choice baked in
+            return CS_OK;
+        }
+    return cs_fail(ctx, CS_E_INVALID, "cs_ctx_set_option: unknown option '%s'", name);
+}
+
 extern "C" int cs_stage_kernel_info(const cs_ctx* ctx, int32_t* last_variant, int64_t* naive_fallbacks) {
     if (!ctx) return cs_fail(ctx, CS_E_INVALID, "cs_stage_kernel_info: NULL context");
     if (last_variant) *last_variant = ctx->last_stage_kernel;

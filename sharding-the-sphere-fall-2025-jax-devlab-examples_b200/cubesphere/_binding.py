@@ -66,6 +66,7 @@ _PROTOTYPES = {
     "cs_halo_push": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_halo_pull": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_scalar_diffuse": (C.c_int, [_VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP]),
+    "cs_ctx_set_option": (C.c_int, [_VP, C.c_char_p, C.c_int]),
     "cs_launch_count": (C.c_int64, [_VP]),
     "cs_step_kernel_trace": (C.c_int, [_VP, C.c_int, C.POINTER(C.c_uint64)]),
     "cs_stage_kernel_info": (C.c_int, [_VP, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]),

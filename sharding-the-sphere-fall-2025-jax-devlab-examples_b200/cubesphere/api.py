@@ -295,6 +295,10 @@ class Context:
     def launches(self):
         return int(self._lib.cs_launch_count(self._h))
 
+    def set_option(self, name, value):
+        """Tuning knob of this context by name (see ``cs_ctx_set_option``)."""
+        self._check(self._lib.cs_ctx_set_option(self._h, name.encode(), int(value)))
+
     def stage_kernel_info(self):
         """(variant name of the last stage launch, number of launches an 'auto' context had to send to the
         one-thread-per-cell kernel because the layout was not vectorisable)."""
