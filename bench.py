@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-secondary", action="store_true", help="skip the fp64 side measurement")
     ap.add_argument("--new-state-sums", action="store_true",
                     help="per-step mass / energy of the NEW state (summed in the last stage) instead of the entry state (first stage)")
+    ap.add_argument("--overlap", default="rim_first", choices=["rim_first", "side", "none"],
+                    help="N > 1: how a stage is split (rim kernel first on the whole GPU, or on a side stream beside the inner kernel)")
     ap.add_argument("--halo-path", default="peer", choices=["peer", "nccl"],
                     help="N > 1: cross-GPU ghosts by one-sided peer stores (CUDA IPC over NVLink) or by pack / NCCL all-to-all / unpack")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the multi-GPU parity run that precedes the timing")
@@ -339,7 +341,8 @@ def run_ours(args):
     # conservation sums every step, taken inside the first stage's launches (the state each step starts from)
     stepper = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
                                      advect_only=case.advect_only, device=local, rank=rank, world=world,
-                                     kernel=args.kernel, sums_of_entry_state=not args.new_state_sums, halo_path=args.halo_path)
+                                     kernel=args.kernel, sums_of_entry_state=not args.new_state_sums, halo_path=args.halo_path,
+                                     overlap=False if args.overlap == "none" else args.overlap)
     assert (stepper.tile_begin, stepper.tile_count) == (t0, tc)
 
     def padded(field):

@@ -37,6 +37,10 @@ class ShardedStepper:
         # sums_of_entry_state: step(..., diag) reports mass / energy of the state the step STARTS from, summed inside
         # the first stage's launches (a few instructions per cell); default: of the new state, inside the last stage's
         self.sums_of_entry_state = bool(sums_of_entry_state)
+        if overlap is True:
+            overlap = "rim_first"
+        if overlap not in (False, "rim_first", "side"):
+            raise ValueError("overlap must be False, True / 'rim_first' or 'side'")
         self.rank, self.world, self.rk, self.overlap, self.group = rank, world, rk, overlap, group
         # world > 1: a step is ~30 host calls (kernel launches, stream waits, one NCCL all-to-all per stage);
         # captured once into a CUDA graph per (dt, state tensors) and replayed, so the host never paces the GPUs
@@ -196,7 +200,7 @@ class ShardedStepper:
         cur = q0
         pairs = RK_PAIRS[self.rk]
         main = torch.cuda.current_stream(self.device)
-        ev_rim = ev_inner = None
+        ev_rim = ev_inner = ev_exch = None
         pending_sums = joined_sums = False
         for k, (a, b) in enumerate(pairs):
             last = k == len(pairs) - 1 and len(pairs) > 1
@@ -204,9 +208,34 @@ class ShardedStepper:
             # the last stage also sums mass / energy of its output -- or the first one those of its input
             sin = self.sums_of_entry_state
             sums = diag is not None and k == (0 if sin else len(pairs) - 1)
-            if self.overlap:
-                # side stream: rim cells -> same-rank ghosts -> pack -> all-to-all -> unpack;
-                # main stream: the inner cells, which is where the time goes.
+            if self.overlap == "rim_first":
+                # main stream: the rim cells first, on the whole GPU (a few microseconds: they are 8 / n of the cells),
+                # then the inner cells; side stream: same-rank ghosts and the cross-GPU exchange of the fresh rim cells,
+                # under the cover of the inner kernel (which leaves it a few SMs).  Only the NEXT stage's rim kernel needs
+                # what the exchange brings, so it has a whole stage of slack; the streams join at the end of the step.
+                if ev_exch is not None:
+                    main.wait_event(ev_exch)                                   # the rim reads remote ghosts of `cur`
+                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=1, diag=self._sums4[2:] if sums else None, sums_of_input=sin)
+                ev_rim = torch.cuda.Event()
+                ev_rim.record(main)
+                with torch.cuda.stream(self.comm_stream):
+                    self.comm_stream.wait_event(ev_rim)
+                    self.ctx.halo_fill_state(*out)
+                    self._exchange(*out)
+                    ev_exch = torch.cuda.Event()
+                    ev_exch.record(self.comm_stream)
+                self.ctx.rk_stage(q0, cur, out, a, b, dt, part=0, diag=self._sums4[:2] if sums else None, sums_of_input=sin)
+                if sums and sin and k < len(pairs) - 1:
+                    # entry-state sums are complete: combine / record them on a stream of their own, under stages 2, 3
+                    ev_inner = torch.cuda.Event()
+                    ev_inner.record(main)
+                    self.sums_stream.wait_event(ev_inner)
+                    with torch.cuda.stream(self.sums_stream):
+                        self._combine_sums(diag)
+                    joined_sums = True
+            elif self.overlap:
+                # (overlap="side", the round-1 arrangement, kept for comparison)
+                # side stream: rim cells -> same-rank ghosts -> exchange; main stream: the inner cells.
                 # Inner cells never read a ghost cell, so stage k+1's inner kernel only waits for stage k's
                 # inner and rim kernels -- not for its exchange, which gets a whole stage of slack and is
                 # needed by stage k+1's rim kernel alone.  The two streams join at the end of the step.
@@ -216,9 +245,6 @@ class ShardedStepper:
                     else:
                         self.comm_stream.wait_event(ev_inner)                  # rim reads inner cells next to it
                         if pending_sums:
-                            # entry-state sums came out of stage 1 (inner + rim kernels, both finished by now): combine
-                            # them across ranks on a stream of their own, under the cover of stages 2 and 3 -- not on
-                            # this one, where the all-reduce would hold up the rim and the exchange behind it
                             self.sums_stream.wait_stream(self.comm_stream)
                             with torch.cuda.stream(self.sums_stream):
                                 self._combine_sums(diag)

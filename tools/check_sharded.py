@@ -19,7 +19,8 @@ torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ok = True
 for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "peer"), (96, 2, True, True, "peer"),
-                                   (96, 2, True, False, "nccl"), (96, 2, False, False, "peer"), (96, 2, False, True, "nccl")):
+                                   (96, 2, True, False, "nccl"), (96, 2, "side", True, "peer"), (96, 2, "side", False, "nccl"),
+                                   (96, 2, False, False, "peer"), (96, 2, False, True, "nccl")):
     if (6 * p * p) % world:
         continue
     g, steps = 2, 10
