@@ -53,7 +53,7 @@ def parse_args():
     ap.add_argument("--no-secondary", action="store_true", help="skip the fp64 side measurement")
     ap.add_argument("--new-state-sums", action="store_true",
                     help="per-step mass / energy of the NEW state (summed in the last stage) instead of the entry state (first stage)")
-    ap.add_argument("--overlap", default="rim_first", choices=["rim_first", "side", "none"],
+    ap.add_argument("--overlap", default="side", choices=["side", "rim_first", "none"],
                     help="N > 1: how a stage is split (rim kernel first on the whole GPU, or on a side stream beside the inner kernel)")
     ap.add_argument("--halo-path", default="peer", choices=["peer", "nccl"],
                     help="N > 1: cross-GPU ghosts by one-sided peer stores (CUDA IPC over NVLink) or by pack / NCCL all-to-all / unpack")
