@@ -57,7 +57,7 @@ class ShardedStepper:
         self._scratch = None
         self._extra_launches = 0
         import os
-        self._sums_where = os.environ.get("CS_SUMS_WHERE", "comm_stream")      # experiment knob: own_stream | comm_stream | skip
+        self._sums_where = os.environ.get("CS_SUMS_WHERE", "own_stream")       # tuning knob: own_stream | comm_stream
         self._skip_exchange = False      # measurement only (time_halo): a step with the cross-GPU exchange left out
         if world > 1:
             self.send_counts, self.recv_counts = self.ctx.halo_plan([b for b, _ in self.ranges],
@@ -291,23 +291,30 @@ class ShardedStepper:
         """Rank-local (inner, rim) sums -> whole sphere: one all-reduce of four doubles, then inner + rim.
         ``diag == "history"``: no collective now -- append the local sums to the on-device record instead."""
         if isinstance(diag, str):
-            self._hist.index_copy_(0, self._hist_idx, self._sums4.unsqueeze(0))
+            self._hist.index_copy_(0, self._hist_idx % self.history_capacity, self._sums4.unsqueeze(0))
             self._hist_idx.add_(1)
             return
         dist.all_reduce(self._sums4, group=self.group)
         torch.add(self._sums4[:2], self._sums4[2:], out=diag)
 
-    def read_sums(self):
-        """Deferred mode: [steps, 2] (mass, energy) of the whole sphere for every step taken with ``diag="history"``
-        since the last call -- one all-reduce for the whole record -- and the record starts again."""
-        n = int(self._hist_idx.item())
-        if n > self.history_capacity:
-            raise RuntimeError(f"{n} steps recorded, the history holds {self.history_capacity}: read it more often")
-        rec = self._hist[:n].clone()
+    def read_sums_async(self):
+        """Deferred mode, no host synchronisation: enqueues ONE all-reduce over the whole on-device record and restarts
+        the record; returns ``(sums [capacity, 2], count [1])`` device tensors -- rows ``[:count]`` are (mass, energy) of
+        the whole sphere for every step taken with ``diag="history"`` since the last read."""
+        rec = self._hist.clone()
+        count = self._hist_idx.clone()
+        self._hist_idx.zero_()
         if self.world > 1:
             dist.all_reduce(rec, group=self.group)
-        self._hist_idx.zero_()
-        return rec[:, :2] + rec[:, 2:]
+        return rec[:, :2] + rec[:, 2:], count
+
+    def read_sums(self):
+        """:meth:`read_sums_async`, then the rows that were recorded, as a ``[steps, 2]`` tensor (synchronises)."""
+        sums, count = self.read_sums_async()
+        n = int(count.item())
+        if n > self.history_capacity:
+            raise RuntimeError(f"{n} steps recorded, the history holds {self.history_capacity}: read it more often")
+        return sums[:n]
 
     def diagnostics(self, h, u, v):
         """[mass, energy] of the whole sphere on every rank (fp64)."""
