@@ -110,7 +110,15 @@ int launch_rim(cs_ctx* ctx, const StageParams<R>& P, double* diag_out, int sums_
 
 template <typename R, int V, int LIM, int MINB>
 int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* diag_out, int sums_in, cudaStream_t s) {
-    const MarchGeom G = march_geometry(ctx, stage_march_kernel<R, V, LIM, MINB, false>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
+    MarchGeom G = march_geometry(ctx, stage_march_kernel<R, V, LIM, MINB, false>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
+    // cs_step asks for the ghosts of an intermediate stage to be pushed by the stage kernel itself (no fill launch)
+    StageParams<R> PP = P;
+    if (ctx->want_post_push && lo == 0 && !P.push && ctx->push_complete && ctx->d_push && !ctx->d_rot && !ctx->d_interp_dst &&
+        ctx->tune.post_push) {
+        G.post_push = 1;
+        PP.push = ctx->d_push;
+        ctx->stage_pushed = true;
+    }
     const int warps = CS_MARCH_THREADS / 32;
     // First stage, (a, b) = (0, 1): a variant compiled without q0 and without the multiplications by b.  11 % fewer
     // instructions in both precisions, but only fp64 gains (169 -> 154 us at C1536); the fp32 build of it is
@@ -120,7 +128,7 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* d
     if (diag_out && !P.push && ctx->tune.fused_diag && G.nitems <= ctx->partial_cap) {
         // last stage of a step: the conservation sums of the output come out of the same launch (K3 fused into K2)
         // ... or, for a first stage, those of its input (the state the step starts from), which cost next to nothing
-        StageParams<R> Q = P;
+        StageParams<R> Q = PP;
         Q.partials = ctx->d_partials, Q.ticket = ctx->d_ticket, Q.diag_out = diag_out, Q.sums_in = sums_in;
         if (!sums_in) {
             CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, false, 1>, grid, block, 0, s, ctx->pdl, Q, G));
@@ -142,12 +150,12 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* d
         bool launched = false;
         if constexpr (sizeof(R) == 8) {
             if (unit_variant && P.a == R(0) && P.b == R(1)) {
-                CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, true>, grid, block, 0, s, ctx->pdl, P, G));
+                CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, true>, grid, block, 0, s, ctx->pdl, PP, G));
                 launched = true;
             }
         }
         if (!launched)
-            CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false>, grid, block, 0, s, ctx->pdl, P, G));
+            CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false>, grid, block, 0, s, ctx->pdl, PP, G));
     }
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
