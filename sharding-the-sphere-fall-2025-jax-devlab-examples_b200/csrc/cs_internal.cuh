@@ -45,7 +45,8 @@ struct CsTuning {
     int tma_ring = 6;            // CS_TMA_RING
     int fused_halo = 1;          // CS_FUSED_HALO: 0 vetoes cfg.fused_halo
     int step_graph = 1;          // CS_STEP_GRAPH: 0 = cs_step enqueues its launches instead of replaying a graph
-    int post_push = 1;           // CS_POST_PUSH: 0 = cs_step fills the ghosts of every stage with the fill kernel
+    int post_push = 0;           // CS_POST_PUSH: 1 = cs_step's intermediate stages push their edge ghosts themselves after the
+                                 // march instead of a fill launch (measured slower: 0.307 vs 0.294 ms per step)
     int step_debug = 0;          // CS_STEP_DEBUG: timing experiments on the step kernel (wrong results)
     int step_kernel = 0;         // CS_STEP_KERNEL: 1 = cs_step uses the one-launch-per-step kernel where it can (measured
                                  // slower than the replayed graph of stage launches at every size: DESIGN.md 4.2)
