@@ -17,6 +17,8 @@ The partition is the reference's: axis 0 block-sharded over a 1-D mesh
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -56,7 +58,6 @@ class ShardedStepper:
         self.n, self.m, self.device = self.ctx.n, self.ctx.m, device
         self._scratch = None
         self._extra_launches = 0
-        import os
         self._sums_where = os.environ.get("CS_SUMS_WHERE", "own_stream")       # tuning knob: own_stream | comm_stream
         self._skip_exchange = False      # measurement only (time_halo): a step with the cross-GPU exchange left out
         if world > 1:
@@ -65,7 +66,10 @@ class ShardedStepper:
             dev = f"cuda:{device}"
             self.sendbuf = torch.zeros(max(1, 3 * sum(self.send_counts)), dtype=self.ctx.dtype, device=dev)
             self.recvbuf = torch.zeros(max(1, 3 * sum(self.recv_counts)), dtype=self.ctx.dtype, device=dev)
-            self.comm_stream = torch.cuda.Stream(device=device)
+            # the side stream has the higher priority: when a stage starts, its short rim kernel is placed on the SMs
+            # before the blocks of the inner kernel, instead of squeezing through the few SMs the inner kernel leaves
+            prio = -1 if os.environ.get("CS_COMM_PRIORITY", "1") != "0" else 0
+            self.comm_stream = torch.cuda.Stream(device=device, priority=prio)
             self.sums_stream = torch.cuda.Stream(device=device)
             self.qa = [self.ctx.new_field() for _ in range(3)]
             self.qb = [self.ctx.new_field() for _ in range(3)]
@@ -87,7 +91,6 @@ class ShardedStepper:
                 self._peer = self._connect_peers()
             self.halo_path = ("peer stores into the neighbours' receive buffers (CUDA IPC over NVLink) + flag, then pull"
                               if self._peer else "pack -> NCCL all_to_all_single -> unpack")
-            import os
             if self._peer and "CS_MARCH_RESERVE_SMS" not in os.environ:
                 # the side stream runs four short kernels of ours and no NCCL kernel: 4 SMs are enough (12 with NCCL);
                 # measured at 2 GPUs, C2176 fp32: 0.307 ms per step with 4, 0.318 with 12
