@@ -123,7 +123,8 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* d
     // First stage, (a, b) = (0, 1): a variant compiled without q0 and without the multiplications by b.  11 % fewer
     // instructions in both precisions, but only fp64 gains (169 -> 154 us at C1536); the fp32 build of it is
     // 7 % SLOWER than the general kernel (87 vs 81 us: a different schedule, not fewer stalls), so fp32 does not use it.
-    const bool unit_variant = ctx->tune.march_unit != 0;
+    // march_unit: 0 never, 1 fp64 only (default), 2 fp32 as well (re-measured after each change of the kernel)
+    const bool unit_variant = sizeof(R) == 8 ? ctx->tune.march_unit >= 1 : ctx->tune.march_unit >= 2;
     const dim3 grid((G.nitems + warps - 1) / warps), block(CS_MARCH_THREADS);
     if (diag_out && !P.push && ctx->tune.fused_diag && G.nitems <= ctx->partial_cap) {
         // last stage of a step: the conservation sums of the output come out of the same launch (K3 fused into K2)
@@ -134,11 +135,9 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* d
             CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, false, 1>, grid, block, 0, s, ctx->pdl, Q, G));
         } else {
             bool launched = false;
-            if constexpr (sizeof(R) == 8) {
-                if (unit_variant && P.a == R(0) && P.b == R(1)) {
-                    CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, true, 2>, grid, block, 0, s, ctx->pdl, Q, G));
-                    launched = true;
-                }
+            if (unit_variant && P.a == R(0) && P.b == R(1)) {
+                CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, true, 2>, grid, block, 0, s, ctx->pdl, Q, G));
+                launched = true;
             }
             if (!launched)
                 CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, false, 2>, grid, block, 0, s, ctx->pdl, Q, G));
@@ -148,11 +147,9 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* d
         CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, true>, grid, block, 0, s, ctx->pdl, P, G));
     } else {
         bool launched = false;
-        if constexpr (sizeof(R) == 8) {
-            if (unit_variant && P.a == R(0) && P.b == R(1)) {
-                CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, true>, grid, block, 0, s, ctx->pdl, PP, G));
-                launched = true;
-            }
+        if (unit_variant && P.a == R(0) && P.b == R(1)) {
+            CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false, true>, grid, block, 0, s, ctx->pdl, PP, G));
+            launched = true;
         }
         if (!launched)
             CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MINB, false>, grid, block, 0, s, ctx->pdl, PP, G));

@@ -101,13 +101,15 @@ __device__ __forceinline__ double march_half_slope<double, CS_LIM_MINMOD>(double
     return dm * dp > 0.0 ? copysign(mag, dm) : 0.0;
 }
 
-// Four times the upwind face flux (the factor 1/4 is folded into MarchConst::kisg); hsL, hsR are half slopes.
-// 2 M (hL + hsL) for M > 0, 2 M (hR - hsR) otherwise: what the oracle's M (l + r) + |M| (l - r) evaluates to, up
-// to one rounding, with the compare and the select on the ALU pipe instead of two more FMA-pipe operations.
+// Twice the upwind face flux (the factor 1/2 is folded into MarchConst::kisg); hsL, hsR are half slopes, M the SUM of
+// the two cells' mass-flux velocities.  M (hL + hsL) for M > 0, M (hR - hsR) otherwise: what the oracle's
+// Fm (l + r) + |Fm| (l - r), Fm = M / 4, evaluates to up to one rounding, with the compare and the select on the ALU
+// pipe instead of two more FMA-pipe operations.  (Scaling by powers of two is exact: carrying 2 F instead of 4 F saves
+// an addition per face and changes no bit of the result.)
 template <typename R>
 __device__ __forceinline__ R march_flux4(R mL, R mR, R hL, R hsL, R hR, R hsR) {
     const R M = mL + mR, left = hL + hsL, right = hR - hsR;
-    return (M + M) * (M > R(0) ? left : right);
+    return M * (M > R(0) ? left : right);
 }
 
 // Constants folded once per thread so that the row loop multiplies as little as possible:
@@ -328,7 +330,7 @@ __device__ __forceinline__ void march_item(const StageParams<R>& P, const MarchG
         const R kf = P.two_omega / P.r2d;
         K.kq = P.ia2 * P.b * P.dt * P.r2d;
         if (P.advect_only) K.kq = R(0);
-        K.kisg = R(0.25) * P.ia2 * P.b * P.dt * P.rd;   // 1/4: fluxes are carried times four
+        K.kisg = R(0.5) * P.ia2 * P.b * P.dt * P.rd;    // 1/2: fluxes are carried times two
         K.kf2 = kf * cf[2];
 #pragma unroll
         for (int c = 0; c < V; ++c) {
@@ -342,6 +344,10 @@ __device__ __forceinline__ void march_item(const StageParams<R>& P, const MarchG
             all_out = all_out && om[c];
         }
     }
+    // Warp-uniform choice of the store path: vector stores when every output lane owns whole groups (the halo lanes
+    // simply do not store); the scalar, masked path only in the two chunks whose edge groups are cut by the range.
+    // (Branching per lane on all_out made every warp run BOTH paths on every row: its two halo lanes took the masked one.)
+    const bool vector_stores = __all_sync(0xffffffffu, all_out || !lane_out);
     // fused halo: only the first / last chunk of a row holds columns within g of the tile's W / E edge.
     // A lane's edge columns share one ghost mapping up to the depth: depth d adds d * ew_dstep elements.
     const bool edge_warp = PUSH && (chunk == 0 || chunk == G.nchunks - 1);
@@ -459,10 +465,12 @@ __device__ __forceinline__ void march_item(const StageParams<R>& P, const MarchG
 
         R oh[V], ou[V], ov[V];
         march_row_update<R, V, LIM, UNIT>(P, K, Dcur, Dnext, hc, uc, vc, dG, c1m, Bnm, Yc, ayc, read_q0, q0h, q0u, q0v, oh, ou, ov);
-        if (all_out) {
-            IO::st(P.ho + oJ, oh);
-            IO::st(P.uo + oJ, ou);
-            IO::st(P.vo + oJ, ov);
+        if (vector_stores) {
+            if (lane_out) {
+                IO::st(P.ho + oJ, oh);
+                IO::st(P.uo + oJ, ou);
+                IO::st(P.vo + oJ, ov);
+            }
         } else {
 #pragma unroll
             for (int c = 0; c < V; ++c)

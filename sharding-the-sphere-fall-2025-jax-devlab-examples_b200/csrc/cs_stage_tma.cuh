@@ -117,7 +117,7 @@ stage_tma_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant
     {
         const R kf = P.two_omega / P.r2d;
         K.kq = P.advect_only ? R(0) : P.ia2 * P.b * P.dt * P.r2d;   // 0 switches the momentum tendencies off
-        K.kisg = R(0.25) * P.ia2 * P.b * P.dt * P.rd;
+        K.kisg = R(0.5) * P.ia2 * P.b * P.dt * P.rd;
         K.kf2 = kf * cf[2];
 #pragma unroll
         for (int c = 0; c < V; ++c) {

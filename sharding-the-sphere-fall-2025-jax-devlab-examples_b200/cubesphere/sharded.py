@@ -66,9 +66,9 @@ class ShardedStepper:
             dev = f"cuda:{device}"
             self.sendbuf = torch.zeros(max(1, 3 * sum(self.send_counts)), dtype=self.ctx.dtype, device=dev)
             self.recvbuf = torch.zeros(max(1, 3 * sum(self.recv_counts)), dtype=self.ctx.dtype, device=dev)
-            # the side stream has the higher priority: when a stage starts, its short rim kernel is placed on the SMs
-            # before the blocks of the inner kernel, instead of squeezing through the few SMs the inner kernel leaves
-            prio = -1 if os.environ.get("CS_COMM_PRIORITY", "1") != "0" else 0
+            # CS_COMM_PRIORITY=1 gives the side stream the higher priority (its short rim kernel is then placed on the
+            # SMs before the blocks of the inner kernel); measured: no gain (2 GPUs 0.299 vs 0.294 ms, 8 GPUs 0.309 vs 0.310)
+            prio = -1 if os.environ.get("CS_COMM_PRIORITY", "0") != "0" else 0
             self.comm_stream = torch.cuda.Stream(device=device, priority=prio)
             self.sums_stream = torch.cuda.Stream(device=device)
             self.qa = [self.ctx.new_field() for _ in range(3)]
@@ -92,9 +92,10 @@ class ShardedStepper:
             self.halo_path = ("peer stores into the neighbours' receive buffers (CUDA IPC over NVLink) + flag, then pull"
                               if self._peer else "pack -> NCCL all_to_all_single -> unpack")
             if self._peer and "CS_MARCH_RESERVE_SMS" not in os.environ:
-                # the side stream runs four short kernels of ours and no NCCL kernel: 4 SMs are enough (12 with NCCL);
-                # measured at 2 GPUs, C2176 fp32: 0.307 ms per step with 4, 0.318 with 12
-                self.ctx.set_option("reserve_sms", 4)
+                # the side stream runs four short kernels of ours and no NCCL kernel: a few SMs are enough (12 with
+                # NCCL).  Measured, C2176 fp32 per GPU: 2 GPUs 0.296 ms per step with 4 SMs, 0.307 with 8; 8 GPUs (seven
+                # peers to wait for, the exchange 33 us instead of 19) 0.306 with 8, 0.310 with 4.
+                self.ctx.set_option("reserve_sms", 4 if world <= 4 else 8)
 
     # -- bookkeeping ------------------------------------------------------------------------
     @property
