@@ -344,10 +344,6 @@ __device__ __forceinline__ void march_item(const StageParams<R>& P, const MarchG
             all_out = all_out && om[c];
         }
     }
-    // Warp-uniform choice of the store path: vector stores when every output lane owns whole groups (the halo lanes
-    // simply do not store); the scalar, masked path only in the two chunks whose edge groups are cut by the range.
-    // (Branching per lane on all_out made every warp run BOTH paths on every row: its two halo lanes took the masked one.)
-    const bool vector_stores = __all_sync(0xffffffffu, all_out || !lane_out);
     // fused halo: only the first / last chunk of a row holds columns within g of the tile's W / E edge.
     // A lane's edge columns share one ghost mapping up to the depth: depth d adds d * ew_dstep elements.
     const bool edge_warp = PUSH && (chunk == 0 || chunk == G.nchunks - 1);
@@ -465,12 +461,13 @@ __device__ __forceinline__ void march_item(const StageParams<R>& P, const MarchG
 
         R oh[V], ou[V], ov[V];
         march_row_update<R, V, LIM, UNIT>(P, K, Dcur, Dnext, hc, uc, vc, dG, c1m, Bnm, Yc, ayc, read_q0, q0h, q0u, q0v, oh, ou, ov);
-        if (vector_stores) {
-            if (lane_out) {
-                IO::st(P.ho + oJ, oh);
-                IO::st(P.uo + oJ, ou);
-                IO::st(P.vo + oJ, ov);
-            }
+        // (per-lane branch on purpose: a warp-uniform choice of the store path -- vector stores predicated on the output
+        // lanes, the masked path only in the edge chunks -- removes the divergence of the two halo lanes and 8 issue
+        // slots per row, and ran stage 1 at 89 us instead of 82 and stages 2 / 3 at 110 instead of 89: DESIGN.md 4.2)
+        if (all_out) {
+            IO::st(P.ho + oJ, oh);
+            IO::st(P.uo + oJ, ou);
+            IO::st(P.vo + oJ, ov);
         } else {
 #pragma unroll
             for (int c = 0; c < V; ++c)
