@@ -55,6 +55,8 @@ def parse_args():
                     help="per-step mass / energy of the NEW state (summed in the last stage) instead of the entry state (first stage)")
     ap.add_argument("--overlap", default="side", choices=["side", "rim_first", "none"],
                     help="N > 1: how a stage is split (rim kernel first on the whole GPU, or on a side stream beside the inner kernel)")
+    ap.add_argument("--tile-map", default="locality", choices=["locality", "block"],
+                    help="N > 1: order of the tiles along the sharded axis (compact blocks, or the reference's plain order)")
     ap.add_argument("--halo-path", default="peer", choices=["peer", "nccl"],
                     help="N > 1: cross-GPU ghosts by one-sided peer stores (CUDA IPC over NVLink) or by pack / NCCL all-to-all / unpack")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the multi-GPU parity run that precedes the timing")
@@ -233,8 +235,7 @@ def multi_gpu_parity(rank, world, local):
 
     def shard(face_field):                                # [6, N, N] interior -> this rank's padded tiles, ghosts zero
         out = np.zeros((c, n + 2 * g, n + 2 * g))
-        for k in range(c):
-            t = b + k
+        for k, t in enumerate(st.tiles):
             f, ty, tx = t // (p * p), (t % (p * p)) // p, t % p
             out[k, g:g + n, g:g + n] = face_field[f, ty * n:(ty + 1) * n, tx * n:(tx + 1) * n]
         return out
@@ -244,7 +245,13 @@ def multi_gpu_parity(rank, world, local):
         for x in tensors:
             parts = [torch.empty_like(x) for _ in range(world)] if rank == 0 else None
             dist.gather(x, parts, dst=0)
-            res.append(torch.cat(parts).cpu().numpy() if rank == 0 else None)
+            if rank == 0:
+                by_pos = torch.cat(parts).cpu().numpy()
+                by_tile = np.empty_like(by_pos)
+                by_tile[st.tile_order] = by_pos              # position k of axis 0 holds tile tile_order[k]
+                res.append(by_tile)
+            else:
+                res.append(None)
         return res
 
     # (1) ghost fill of random numbers, bit for bit
@@ -332,7 +339,8 @@ def run_ours(args):
     t0, tc = ranges[rank]
     # every rank builds only its own tiles of the initial condition (interior cells [tc, n, n])
     from cubesphere import cases
-    case = cases.make_case(args.case, N, p=p, tiles=range(t0, t0 + tc))
+    order = partition.locality_order(p, world) if (args.tile_map == "locality" and world > 1) else np.arange(6 * p * p)
+    case = cases.make_case(args.case, N, p=p, tiles=[int(t) for t in order[t0:t0 + tc]])
     dt = cases.stable_dt(case, 0.5)
     if world > 1:
         tdt = torch.tensor([dt], device="cuda", dtype=torch.float64)
@@ -342,7 +350,7 @@ def run_ours(args):
     stepper = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
                                      advect_only=case.advect_only, device=local, rank=rank, world=world,
                                      kernel=args.kernel, sums_of_entry_state=not args.new_state_sums, halo_path=args.halo_path,
-                                     overlap=False if args.overlap == "none" else args.overlap)
+                                     overlap=False if args.overlap == "none" else args.overlap, tile_map=args.tile_map)
     assert (stepper.tile_begin, stepper.tile_count) == (t0, tc)
 
     def padded(field):
@@ -474,7 +482,8 @@ def run_ours(args):
             # the comparison arm: the same job with pack -> NCCL all-to-all -> unpack
             alt = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
                                          advect_only=case.advect_only, device=local, rank=rank, world=world,
-                                         kernel=args.kernel, sums_of_entry_state=not args.new_state_sums, halo_path="nccl")
+                                         kernel=args.kernel, sums_of_entry_state=not args.new_state_sums, halo_path="nccl",
+                                         tile_map=args.tile_map)
             adev = [x.clone() for x in dev]
             alt.halo_fill(*adev)
             for _ in range(5):
@@ -585,6 +594,8 @@ def run_ours(args):
             "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": f"{args.case} C{N}, SSP-RK3 (3 fused stages + halo + mass/energy sums) per step, {args.dtype}",
                        "N": N, "tiles_per_edge": p, "halo": g, "tiles_per_gpu": tc, "parallelism": f"tiles/{world}",
+                       "tile_map": stepper.tile_map + (f": {partition.cut_edges(stepper.tile_order, p, world)} of {12 * p * p} tile edges cross GPUs"
+                                                       if world > 1 else ""),
                        "reductions": ("mass and energy every step: of the new state, summed inside the last stage launch"
                                       if args.new_state_sums else
                                       "mass and energy every step: of the state the step starts from, summed inside the first stage launch")

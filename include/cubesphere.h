@@ -26,10 +26,11 @@
  * State layout (reference JAX-DevLab-Examples.py:141,174; deck slide 11):
  *   each field is one dense array  [tile_count][n + 2g][n + 2g], x fastest,
  *   n = N / tiles_per_edge, interior cells at [g, g + n) on both axes, tile id =
- *   face * p^2 + ty * p + tx.  A context owns the contiguous tile range
- *   [tile_begin, tile_begin + tile_count) -- the block partition of axis 0 that
+ *   face * p^2 + ty * p + tx.  A context owns the contiguous range of POSITIONS
+ *   [tile_begin, tile_begin + tile_count) of axis 0 -- the block partition that
  *   the reference gets from NamedSharding(mesh, P('tiles'))
- *   (JAX-DevLab-Examples.py:77-79).  h is the fluid depth (m); u, v are the
+ *   (JAX-DevLab-Examples.py:77-79); position k holds tile k unless cs_config.tile_order
+ *   says otherwise.  h is the fluid depth (m); u, v are the
  *   panel-local contravariant velocity components (rad/s).
  *
  * "Replaces" below cites the reference interface each entry point stands in for
@@ -99,7 +100,10 @@ typedef struct cs_config {
                                   *    launch); 1: of the state the step STARTS from (summed inside the first stage launch,
                                   *    where it costs a few instructions per cell and no registers: state n's sums arrive
                                   *    with step n + 1, and a final cs_diagnostics gives the last state's) */
-    int32_t reserved[2];
+    const int32_t* tile_order;/* optional host table of 6 p^2 entries: position along axis 0 -> tile id (face p^2 + ty p + tx), */
+                              /* a permutation.  tile_begin / tile_count (and the peers of cs_halo_plan) then count POSITIONS, */
+                              /* so a block partition of axis 0 can hand each device a spatially compact set of tiles          */
+                              /* (cubesphere.partition.locality_order).  NULL -> identity.  (Occupies the former reserved[2].)  */
     double radius;            /* a      (0 -> 6.37122e6 m)                                   */
     double omega;             /* Omega  (0 -> 7.292e-5 1/s; set advect_only for no rotation) */
     double gravity;           /* g      (0 -> 9.80616 m/s^2)                                 */

@@ -32,7 +32,8 @@ struct StageParams {
     unsigned int* ticket;     // ... its completion counter (zero between launches)
     double* diag_out;         // ... and where [mass, energy] go
     int sums_in;              // the sums are those of the stage INPUT (qs) instead of the output
-    int n, g, m, p, T, t0;
+    const int32_t* tile_ids;  // [T] tile id (face p^2 + ty p + tx) of every owned position
+    int n, g, m, p, T;
     int part;                 // 0 inner cells, 1 rim, 2 all
     int advect_only;
     R a, b, dt;               // out = a q0 + b (qs + dt L(qs)); a == 0 -> q0 is not read
@@ -154,7 +155,7 @@ struct CellOut {
 template <typename R, int LIM>
 CS_HD void cs_stage_cell(const StageParams<R>& P, int t, int j, int i, CellOut<R>* out = nullptr) {
     const int m = P.m, g = P.g;
-    const TileCoord tc = cs_tile_coord(t + P.t0, P.p);
+    const TileCoord tc = cs_tile_coord(P.tile_ids[t], P.p);
     const R* xt = P.xt + tc.tx * P.n;
     const R* yt = P.xt + tc.ty * P.n;
     const int jt = j + g, it = i + g;

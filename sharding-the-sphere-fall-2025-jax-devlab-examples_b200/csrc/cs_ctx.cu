@@ -159,6 +159,17 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
     ctx->cfg.tangents = nullptr;
     ctx->N = N, ctx->p = p, ctx->n = n, ctx->g = g, ctx->m = m;
     ctx->T_all = T_all, ctx->t0 = cfg->tile_begin, ctx->T = T;
+    ctx->order.resize(T_all), ctx->inv.assign(T_all, -1);
+    for (int k = 0; k < T_all; ++k) ctx->order[k] = cfg->tile_order ? cfg->tile_order[k] : k;
+    for (int k = 0; k < T_all; ++k) {
+        const int t = ctx->order[k];
+        if (t < 0 || t >= T_all || ctx->inv[t] >= 0) {
+            delete ctx;
+            return cs_fail(nullptr, CS_E_INVALID, "tile_order is not a permutation of 0 .. %d (entry %d = %d)", T_all - 1, k, t);
+        }
+        ctx->inv[t] = k;
+    }
+    ctx->cfg.tile_order = nullptr;
     ctx->dtype = cfg->dtype, ctx->esize = esize, ctx->device = cfg->device;
     ctx->field_elems = (size_t)T * m * m;
     ctx->pitch16 = ((size_t)m * esize) % 16 == 0;   // vectorised / TMA stage kernels need it
@@ -184,6 +195,10 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
 
     int rc;
     if ((rc = build_tables(ctx, cfg->tangents))) return bail(rc);
+    if (cudaMalloc((void**)&ctx->d_tile_ids, (size_t)T * sizeof(int32_t)) != cudaSuccess)
+        return bail(cs_fail(ctx, CS_E_NOMEM, "cudaMalloc of the tile table failed"));
+    if (cudaMemcpy(ctx->d_tile_ids, ctx->order.data() + ctx->t0, (size_t)T * sizeof(int32_t), cudaMemcpyHostToDevice) != cudaSuccess)
+        return bail(cs_fail(ctx, CS_E_CUDA, "upload of the tile table failed"));
     if ((rc = cs_build_halo(ctx))) return bail(rc);
     const size_t bytes = ctx->field_elems * esize;
     if (g >= 2) {
@@ -247,7 +262,7 @@ extern "C" int cs_ctx_destroy(cs_ctx* ctx) {
         if (ctx->pipe.state[1][k]) cudaFree(ctx->pipe.state[1][k]);
     if (ctx->pipe.diag) cudaFree(ctx->pipe.diag);
     if (ctx->pipe.diag_pinned) cudaFreeHost(ctx->pipe.diag_pinned);
-    void* ptrs[] = {ctx->d_xt, ctx->d_ainv, ctx->d_xt64, ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, ctx->d_rot, ctx->d_push, ctx->d_interp_dst, ctx->d_interp_src, ctx->d_interp_w, ctx->d_interp_rot,
+    void* ptrs[] = {ctx->d_xt, ctx->d_ainv, ctx->d_xt64, ctx->d_halo_dst, ctx->d_halo_src, ctx->d_halo_code, ctx->d_rot, ctx->d_push, ctx->d_tile_ids, ctx->d_interp_dst, ctx->d_interp_src, ctx->d_interp_w, ctx->d_interp_rot,
                     ctx->d_send_src, ctx->d_recv_dst, ctx->d_recv_code, ctx->d_send_off, ctx->d_recv_off, ctx->qa[0], ctx->qa[1], ctx->qa[2],
                     ctx->qb[0], ctx->qb[1], ctx->qb[2], ctx->topo, ctx->host_state[0], ctx->host_state[1], ctx->host_state[2], ctx->d_partials, ctx->d_diag, ctx->d_ticket};
     for (void* q : ptrs)

@@ -15,7 +15,7 @@ constexpr int DIAG_UNROLL = 4;
 template <typename R>
 __global__ void __launch_bounds__(DIAG_THREADS)
 diag_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restrict__ v, const R* __restrict__ topo,
-            const double* __restrict__ xt, int n, int g, int m, int p, int T, int t0, int rows_per_block, double a2, double grav,
+            const double* __restrict__ xt, int n, int g, int m, int p, int T, const int32_t* __restrict__ tile_ids, int rows_per_block, double a2, double grav,
             double darea,
             double* __restrict__ partials, unsigned int* __restrict__ ticket, double* __restrict__ out) {
     // a block owns `rows_per_block` consecutive rows of one tile (no integer division per cell);
@@ -26,7 +26,7 @@ diag_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restric
         const int t = b / blocks_per_tile;
         const int j0 = (b - t * blocks_per_tile) * rows_per_block;
         const int j1 = min(j0 + rows_per_block, n);
-        const TileCoord tc = cs_tile_coord(t + t0, p);
+        const TileCoord tc = cs_tile_coord(tile_ids[t], p);
         const double* xt_x = xt + tc.tx * n + g;
         const double* xt_y = xt + tc.ty * n + g;
         for (int j = j0; j < j1; ++j) {
@@ -78,12 +78,12 @@ int cs_launch_diag(cs_ctx* ctx, const void* h, const void* u, const void* v, dou
     if (ctx->dtype == CS_F64)
         diag_kernel<double><<<(int)blocks, DIAG_THREADS, 0, s>>>((const double*)h, (const double*)u, (const double*)v,
                                                                 ctx->has_topo ? (const double*)ctx->topo : nullptr, ctx->d_xt64,
-                                                                ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, rows_per_block, a2,
+                                                                ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->d_tile_ids, rows_per_block, a2,
                                                                 ctx->gravity, darea, ctx->d_partials + 4 * (size_t)ctx->partial_cap, ctx->d_ticket + 2, out);
     else
         diag_kernel<float><<<(int)blocks, DIAG_THREADS, 0, s>>>((const float*)h, (const float*)u, (const float*)v,
                                                                ctx->has_topo ? (const float*)ctx->topo : nullptr, ctx->d_xt64,
-                                                               ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->t0, rows_per_block, a2,
+                                                               ctx->n, ctx->g, ctx->m, ctx->p, ctx->T, ctx->d_tile_ids, rows_per_block, a2,
                                                                ctx->gravity, darea, ctx->d_partials + 4 * (size_t)ctx->partial_cap, ctx->d_ticket + 2, out);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());

@@ -61,7 +61,13 @@ struct cs_ctx {
     cs_peer_state* peer = nullptr;
     CsTuning tune;
     int N = 0, p = 0, n = 0, g = 0, m = 0;
-    int T_all = 0, t0 = 0, T = 0;
+    int T_all = 0, t0 = 0, T = 0;                // t0, T: first POSITION along axis 0 and number of positions owned
+    std::vector<int32_t> order, inv;             // position -> tile id (cfg.tile_order or the identity) and its inverse
+    int32_t* d_tile_ids = nullptr;               // [T] tile ids of the owned positions
+    int local_index(int tile) const {            // index of a tile inside this context's shard, or -1
+        const int pos = inv[tile];
+        return pos >= t0 && pos < t0 + T ? pos - t0 : -1;
+    }
     int dtype = CS_F64;
     size_t esize = 8;
     int device = 0, num_sms = 148;

@@ -18,12 +18,12 @@ namespace {
 template <typename R>
 __global__ void __launch_bounds__(256)
 diffuse_kernel(const R* __restrict__ T, R* __restrict__ out, const R* __restrict__ src, const double* __restrict__ xt, int n, int g,
-               int m, int p, int t0, double a2, double kdt_over_d2, double dts) {
+               int m, int p, const int32_t* __restrict__ tile_ids, double a2, double kdt_over_d2, double dts) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
     const int t = blockIdx.z;
     if (i >= n || j >= n) return;
-    const TileCoord tc = cs_tile_coord(t + t0, p);
+    const TileCoord tc = cs_tile_coord(tile_ids[t], p);
     const double* xx = xt + tc.tx * n + g + i;            // tangents at columns i-1, i, i+1 (ghosts: periodic table)
     const double* yy = xt + tc.ty * n + g + j;
     const size_t o = (size_t)t * m * m + (size_t)(j + g) * m + (i + g);
@@ -55,10 +55,10 @@ extern "C" int cs_scalar_diffuse(cs_ctx* ctx, const void* T, void* Tout, const v
     const double a2 = ctx->radius * ctx->radius, k = kappa_dt / (ctx->delta * ctx->delta);
     if (ctx->dtype == CS_F64)
         diffuse_kernel<double><<<grid, block, 0, s>>>((const double*)T, (double*)Tout, (const double*)source, ctx->d_xt64, ctx->n, ctx->g,
-                                                     ctx->m, ctx->p, ctx->t0, a2, k, dt_source);
+                                                     ctx->m, ctx->p, ctx->d_tile_ids, a2, k, dt_source);
     else
         diffuse_kernel<float><<<grid, block, 0, s>>>((const float*)T, (float*)Tout, (const float*)source, ctx->d_xt64, ctx->n, ctx->g,
-                                                    ctx->m, ctx->p, ctx->t0, a2, k, dt_source);
+                                                    ctx->m, ctx->p, ctx->d_tile_ids, a2, k, dt_source);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return cs_launch_halo(ctx, Tout, nullptr, nullptr, 1, s);      // local ghosts; a sharded caller exchanges the rest

@@ -138,15 +138,17 @@ int cs_build_halo(cs_ctx* ctx) {
     const int m = ctx->m;
     const int64_t tile_elems = (int64_t)m * m;
     ctx->halo.clear();
-    for (int t = ctx->t0; t < ctx->t0 + ctx->T; ++t) {
-        const int64_t base = (int64_t)(t - ctx->t0) * tile_elems;
+    for (int k = 0; k < ctx->T; ++k) {
+        const int t = ctx->order[ctx->t0 + k];
+        const int64_t base = (int64_t)k * tile_elems;
         for_each_ghost(t, ctx->N, ctx->p, ctx->g, [&](int jt, int it, int ts, int32_t src_local, int code) {
             HaloEntry e;
             e.dst = base + (int64_t)jt * m + it;
             e.src_tile = ts;
             e.src_local = src_local;
             e.code = code;
-            e.src = (ts >= ctx->t0 && ts < ctx->t0 + ctx->T) ? (int64_t)(ts - ctx->t0) * tile_elems + src_local : -1;
+            const int li = ctx->local_index(ts);
+            e.src = li >= 0 ? (int64_t)li * tile_elems + src_local : -1;
             ctx->halo.push_back(e);
         });
     }
@@ -168,7 +170,8 @@ int cs_build_halo(cs_ctx* ctx) {
     const int p = ctx->p;
     std::vector<int4> push((size_t)ctx->T * 4);
     ctx->push_complete = true;
-    for (int t = ctx->t0; t < ctx->t0 + ctx->T; ++t) {
+    for (int k = 0; k < ctx->T; ++k) {
+        const int t = ctx->order[ctx->t0 + k];
         const int face = t / (p * p), ty = (t % (p * p)) / p, tx = t % p;
         for (int e = 0; e < 4; ++e) {
             const bool inside = e == 0 ? ty < p - 1 : e == 1 ? ty > 0 : e == 2 ? tx < p - 1 : tx > 0;
@@ -189,9 +192,9 @@ int cs_build_halo(cs_ctx* ctx) {
                 rev = s.rev;
                 code_ = back.code;
             }
-            const bool local = dt_ >= ctx->t0 && dt_ < ctx->t0 + ctx->T;
-            if (!local) ctx->push_complete = false;
-            push[(size_t)(t - ctx->t0) * 4 + e] = make_int4(local ? dt_ - ctx->t0 : -1, de, rev, code_);
+            const int li = ctx->local_index(dt_);
+            if (li < 0) ctx->push_complete = false;
+            push[(size_t)k * 4 + e] = make_int4(li, de, rev, code_);
         }
     }
     return upload(ctx, &ctx->d_push, push);
@@ -199,11 +202,16 @@ int cs_build_halo(cs_ctx* ctx) {
 
 int cs_build_peer_plan(cs_ctx* ctx, int n_peers, const int32_t* tb, const int32_t* tc) {
     if (n_peers < 1 || !tb || !tc) return cs_fail(ctx, CS_E_INVALID, "cs_halo_plan: need at least one peer");
+    // peers are ranges of POSITIONS along axis 0; a tile belongs to the peer whose range holds its position
     auto owner = [&](int tile) {
+        const int pos = ctx->inv[tile];
         for (int r = 0; r < n_peers; ++r)
-            if (tile >= tb[r] && tile < tb[r] + tc[r]) return r;
+            if (pos >= tb[r] && pos < tb[r] + tc[r]) return r;
         return -1;
     };
+    for (int r = 0; r < n_peers; ++r)
+        if (tb[r] < 0 || tc[r] < 0 || tb[r] + tc[r] > ctx->T_all)
+            return cs_fail(ctx, CS_E_INVALID, "cs_halo_plan: peer %d owns positions [%d, %d), outside [0, %d)", r, tb[r], tb[r] + tc[r], ctx->T_all);
     ctx->peers.assign(n_peers, PeerPlan());
     std::vector<std::vector<int32_t>> send_src(n_peers), recv_dst(n_peers);
     std::vector<std::vector<uint8_t>> recv_code(n_peers);
@@ -221,10 +229,10 @@ int cs_build_peer_plan(cs_ctx* ctx, int n_peers, const int32_t* tb, const int32_
         ctx->peers[r].tile_begin = tb[r];
         ctx->peers[r].tile_count = tc[r];
         if (tb[r] == ctx->t0 && tc[r] == ctx->T) continue;   // ourselves
-        for (int t = tb[r]; t < tb[r] + tc[r]; ++t)
-            for_each_ghost(t, ctx->N, ctx->p, ctx->g, [&](int, int, int ts, int32_t src_local, int) {
-                if (ts >= ctx->t0 && ts < ctx->t0 + ctx->T && !(ts >= tb[r] && ts < tb[r] + tc[r]))
-                    send_src[r].push_back((int32_t)((int64_t)(ts - ctx->t0) * tile_elems + src_local));
+        for (int pos = tb[r]; pos < tb[r] + tc[r]; ++pos)
+            for_each_ghost(ctx->order[pos], ctx->N, ctx->p, ctx->g, [&](int, int, int ts, int32_t src_local, int) {
+                const int li = ctx->local_index(ts);
+                if (li >= 0 && owner(ts) != r) send_src[r].push_back((int32_t)((int64_t)li * tile_elems + src_local));
             });
     }
     std::vector<int32_t> all_send, all_recv;

@@ -28,7 +28,7 @@ class CsConfig(C.Structure):
         ("abi_version", C.c_int32), ("N", C.c_int32), ("tiles_per_edge", C.c_int32), ("halo", C.c_int32),
         ("dtype", C.c_int32), ("rk", C.c_int32), ("limiter", C.c_int32), ("advect_only", C.c_int32),
         ("device", C.c_int32), ("tile_begin", C.c_int32), ("tile_count", C.c_int32), ("kernel", C.c_int32),
-        ("fused_halo", C.c_int32), ("sums_of_entry_state", C.c_int32), ("reserved", C.c_int32 * 2),
+        ("fused_halo", C.c_int32), ("sums_of_entry_state", C.c_int32), ("tile_order", C.POINTER(C.c_int32)),
         ("radius", C.c_double), ("omega", C.c_double), ("gravity", C.c_double), ("axis", C.c_double * 3),
         ("tangents", C.POINTER(C.c_double)),
     ]

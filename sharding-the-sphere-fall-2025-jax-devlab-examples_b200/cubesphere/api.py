@@ -219,7 +219,7 @@ class Context:
 
     def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f64", rk="ssprk3", limiter="mc", advect_only=False,
                  device=0, tile_begin=0, tile_count=0, kernel="auto", fused_halo=False, radius=0.0, omega=0.0,
-                 gravity=0.0, axis=(0.0, 0.0, 1.0), tangents=None, sums_of_entry_state=False):
+                 gravity=0.0, axis=(0.0, 0.0, 1.0), tangents=None, sums_of_entry_state=False, tile_order=None):
         self._lib = B.lib()
         self.dtype = _torch_dtype(dtype)
         if rk not in B.RK_IDS:
@@ -246,6 +246,15 @@ class Context:
             if self._tangents.shape != (int(N),):
                 raise ValueError(f"tangents must have shape ({N},)")
             cfg.tangents = self._tangents.ctypes.data_as(C.POINTER(C.c_double))
+        # tile_order: position along axis 0 -> tile id (a permutation of range(6 p^2)); tile_begin / tile_count then
+        # count positions.  None = identity (the reference's plain block order).
+        n_all = topology.num_tiles(int(tiles_per_edge))
+        self.tile_order = np.arange(n_all, dtype=np.int32)
+        if tile_order is not None:
+            self.tile_order = np.ascontiguousarray(tile_order, dtype=np.int32)
+            if self.tile_order.shape != (n_all,):
+                raise ValueError(f"tile_order must have {n_all} entries")
+            cfg.tile_order = self.tile_order.ctypes.data_as(C.POINTER(C.c_int32))
         handle = C.c_void_p()
         B.check(self._lib.cs_ctx_create(C.byref(cfg), C.byref(handle)))
         self._h = handle
@@ -255,6 +264,7 @@ class Context:
         self.device = int(device)
         self.tile_begin = int(tile_begin)
         self.tile_count = int(tile_count) or topology.num_tiles(self.p)
+        self.tiles = self.tile_order[self.tile_begin:self.tile_begin + self.tile_count].copy()   # tile ids owned, in order
         self.shape = (self.tile_count, self.m, self.m)
 
     # -- plumbing -------------------------------------------------------------

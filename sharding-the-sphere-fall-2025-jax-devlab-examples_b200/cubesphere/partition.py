@@ -30,6 +30,90 @@ def block_ranges(num_tiles: int, world: int):
     return [(r * per, per) for r in range(world)]
 
 
+def tile_adjacency(p: int):
+    """[(tile_a, tile_b)] for the 12 p^2 tile edges of the sphere (each once, a < b)."""
+    desc = topology.edge_push_descriptors(p)
+    edges = set()
+    for t in range(desc.shape[0]):
+        for e in range(4):
+            a, b = t, int(desc[t, e, 0])
+            edges.add((min(a, b), max(a, b)))
+    return sorted(edges)
+
+
+def cut_edges(order, p: int, world: int):
+    """Number of tile edges whose two tiles lie on different devices when axis 0, in this order, is block-partitioned."""
+    n = topology.num_tiles(p)
+    per = n // world
+    owner = np.empty(n, dtype=np.int64)
+    owner[np.asarray(order)] = np.arange(n) // per
+    return sum(1 for a, b in tile_adjacency(p) if owner[a] != owner[b])
+
+
+def locality_order(p: int, world: int, restarts: int = 64, seed: int = 20251118):
+    """A permutation of the tiles along axis 0 whose plain block partition over ``world`` devices cuts few tile edges:
+    the reference's ``P('tiles')`` contract (JAX-DevLab-Examples.py:77-79) is kept -- equal contiguous blocks of axis 0
+    -- and only the ORDER of the tiles along the axis changes (the deck's "Graph Partitioner" box, slide 7).
+
+    Deterministic local search (pairwise swaps between devices, random restarts with a fixed seed, ties broken by the
+    smaller permutation), so every rank computes the same answer.  For 24 tiles on 8 devices it finds the obvious optimum:
+    every device owns the three tiles around one cube vertex (24 of 48 edges cut instead of 36 for the block order, and
+    three neighbour devices each instead of up to seven); on 4 devices 16 instead of 26.
+    """
+    n = topology.num_tiles(p)
+    if n % world:
+        raise ValueError(f"{n} tiles cannot be split evenly over {world} devices")
+    per = n // world
+    if world == 1 or per == 1:
+        return np.arange(n, dtype=np.int32)
+    edges = tile_adjacency(p)
+    nbr = [[] for _ in range(n)]
+    for a, b in edges:
+        nbr[a].append(b)
+        nbr[b].append(a)
+    rng = np.random.default_rng(seed)
+
+    def cut(owner):
+        return sum(1 for a, b in edges if owner[a] != owner[b])
+
+    def gain(owner, t, new):                    # change of the cut when tile t moves to device `new`
+        old = owner[t]
+        return sum(int(owner[q] == old) - int(owner[q] == new) for q in nbr[t])
+
+    best_owner, best_cut = None, None
+    for r in range(restarts):
+        owner = [int(x) for x in np.arange(n) // per]
+        if r:
+            owner = [owner[k] for k in rng.permutation(n)]
+        improved = True
+        while improved:
+            improved = False
+            for a in range(n):
+                for b in range(a + 1, n):
+                    if owner[a] == owner[b]:
+                        continue
+                    oa, ob = owner[a], owner[b]
+                    d = gain(owner, a, ob)
+                    owner[a] = ob
+                    d += gain(owner, b, oa)
+                    owner[b] = oa
+                    if d < 0:
+                        improved = True
+                    else:
+                        owner[a], owner[b] = oa, ob
+        c = cut(owner)
+        # canonical labelling: devices numbered by their smallest tile, so equal partitions compare equal
+        first = {}
+        for t in range(n):
+            first.setdefault(owner[t], len(first))
+        canon = np.array([first[o] for o in owner])
+        key = (c, tuple(canon))
+        if best_cut is None or key < best_cut:
+            best_cut, best_owner = key, canon
+    order = np.concatenate([np.nonzero(best_owner == d)[0] for d in range(world)]).astype(np.int32)
+    return order
+
+
 class ExchangePlan:
     """Send / receive index lists of one rank.
 
@@ -39,19 +123,29 @@ class ExchangePlan:
     All offsets are element offsets into the local shard ``[tile_count, m, m]``.
     """
 
-    def __init__(self, N, p, g, rank, ranges):
+    def __init__(self, N, p, g, rank, ranges, order=None):
+        """``ranges``: (begin, count) of every rank in POSITIONS along axis 0; ``order``: position -> tile id
+        (default: the identity, i.e. the reference's block order)."""
         self.N, self.p, self.g, self.rank, self.ranges = N, p, g, rank, list(ranges)
         n = N // p
         m = n + 2 * g
-        tab = topology.build_halo_table(N, p, g)
+        n_all = topology.num_tiles(p)
+        order = np.arange(n_all) if order is None else np.asarray(order, dtype=np.int64)
+        pos_of = np.empty(n_all, dtype=np.int64)
+        pos_of[order] = np.arange(n_all)
+        # ghost cells in the order the library enumerates them: position by position
+        tab0 = topology.build_halo_table(N, p, g)
+        per_tile = tab0["dst_tile"].size // n_all
+        sel = np.concatenate([np.arange(t * per_tile, (t + 1) * per_tile) for t in order])
+        tab = {k: v[sel] for k, v in tab0.items()}
         t0, tc = self.ranges[rank]
-        owner_of = np.empty(topology.num_tiles(p), dtype=np.int64)
+        owner_of = np.empty(n_all, dtype=np.int64)
         for r, (b, c) in enumerate(self.ranges):
-            owner_of[b:b + c] = r
+            owner_of[order[b:b + c]] = r
         dst_owner = owner_of[tab["dst_tile"]]
         src_owner = owner_of[tab["src_tile"]]
-        dst_off = (tab["dst_tile"] - t0) * m * m + tab["dst_j"] * m + tab["dst_i"]
-        src_off_mine = (tab["src_tile"] - t0) * m * m + tab["src_j"] * m + tab["src_i"]
+        dst_off = (pos_of[tab["dst_tile"]] - t0) * m * m + tab["dst_j"] * m + tab["dst_i"]
+        src_off_mine = (pos_of[tab["src_tile"]] - t0) * m * m + tab["src_j"] * m + tab["src_i"]
         mine = dst_owner == rank
         loc = mine & (src_owner == rank)
         self.local_dst, self.local_src, self.local_code = dst_off[loc], src_off_mine[loc], tab["code"][loc]

@@ -23,7 +23,7 @@ import torch
 import torch.distributed as dist
 
 from . import api, topology
-from .partition import block_ranges
+from .partition import block_ranges, locality_order
 
 RK_PAIRS = {
     "euler": ((0.0, 1.0),),
@@ -35,7 +35,7 @@ RK_PAIRS = {
 class ShardedStepper:
     def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f32", rk="ssprk3", limiter="mc", advect_only=False,
                  axis=(0.0, 0.0, 1.0), device=0, rank=0, world=1, kernel="auto", tangents=None, overlap=True,
-                 group=None, use_graph=True, sums_of_entry_state=False, halo_path="peer"):
+                 group=None, use_graph=True, sums_of_entry_state=False, halo_path="peer", tile_map="locality"):
         # sums_of_entry_state: step(..., diag) reports mass / energy of the state the step STARTS from, summed inside
         # the first stage's launches (a few instructions per cell); default: of the new state, inside the last stage's
         self.sums_of_entry_state = bool(sums_of_entry_state)
@@ -50,12 +50,23 @@ class ShardedStepper:
         self._graphs = {}
         self._eager_calls = {}
         self.ranges = block_ranges(topology.num_tiles(tiles_per_edge), world)
-        self.tile_begin, self.tile_count = self.ranges[rank]
+        self.tile_begin, self.tile_count = self.ranges[rank]          # positions along axis 0 (the P('tiles') blocks)
+        # which tile sits at which position: "block" = the reference's order (tile k at position k), "locality" = an
+        # order whose blocks are spatially compact (fewer tile edges, and fewer peers, across GPUs), or an explicit table
+        if isinstance(tile_map, str):
+            if tile_map not in ("block", "locality"):
+                raise ValueError("tile_map must be 'block', 'locality' or a permutation of the tile ids")
+            order = locality_order(tiles_per_edge, world) if tile_map == "locality" and world > 1 else None
+        else:
+            order = tile_map
+        self.tile_map = "block" if order is None else "locality" if isinstance(tile_map, str) else "custom"
         self.ctx = api.Context(N, tiles_per_edge=tiles_per_edge, halo=halo, dtype=dtype, rk=rk, limiter=limiter,
                                advect_only=advect_only, axis=axis, device=device, kernel=kernel, tangents=tangents,
-                               sums_of_entry_state=sums_of_entry_state,
+                               sums_of_entry_state=sums_of_entry_state, tile_order=order,
                                tile_begin=self.tile_begin, tile_count=self.tile_count if world > 1 else 0)
         self.n, self.m, self.device = self.ctx.n, self.ctx.m, device
+        self.tiles = [int(t) for t in self.ctx.tiles]                   # tile ids of this rank's shard, in shard order
+        self.tile_order = self.ctx.tile_order
         self._scratch = None
         self._extra_launches = 0
         self._sums_where = os.environ.get("CS_SUMS_WHERE", "own_stream")       # tuning knob: own_stream | comm_stream

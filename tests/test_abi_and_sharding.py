@@ -86,9 +86,14 @@ def test_product_never_imports_oracle():
             not re.search(r"^\s*(from|import)\s+oracle|#include\s+\".*oracle", text, flags=re.M), f
 
 
+@pytest.mark.parametrize("tile_map", ["block", "locality", "shuffled"])
 @pytest.mark.parametrize("N,p,world", [(8, 1, 2), (8, 2, 4), (12, 2, 8), (8, 1, 6)])
-def test_exchange_plan_serial_emulation(N, p, world):
-    """All ranks emulated in one process: local fill + pack/exchange/unpack == face-level oracle fill."""
+def test_exchange_plan_serial_emulation(N, p, world, tile_map):
+    """All ranks emulated in one process: local fill + pack/exchange/unpack == face-level oracle fill, whatever the
+    order of the tiles along the sharded axis (the reference's block order, the compact blocks of locality_order, or
+    any permutation)."""
+    order = {"block": np.arange(6 * p * p), "locality": partition.locality_order(p, world),
+             "shuffled": np.random.default_rng(3).permutation(6 * p * p)}[tile_map]
     g = 2
     rng = np.random.default_rng(7)
     M = N + 2 * g
@@ -102,8 +107,8 @@ def test_exchange_plan_serial_emulation(N, p, world):
         w[:, g:g + n, g:g + n] = t[:, g:g + n, g:g + n]
         tiles.append(w)
     ranges = partition.block_ranges(6 * p * p, world)
-    plans = [partition.ExchangePlan(N, p, g, r, ranges) for r in range(world)]
-    shards = [[np.ascontiguousarray(x[b:b + c]) for x in tiles] for b, c in ranges]
+    plans = [partition.ExchangePlan(N, p, g, r, ranges, order) for r in range(world)]
+    shards = [[np.ascontiguousarray(x[order[b:b + c]]) for x in tiles] for b, c in ranges]
     for r in range(world):
         for q in range(world):
             assert plans[r].send_counts[q] == plans[q].recv_counts[r]
@@ -113,7 +118,31 @@ def test_exchange_plan_serial_emulation(N, p, world):
         pl.unpack([packed[q][r] for q in range(world)], sh)
         b, c = ranges[r]
         for got, want in zip(sh, ref):
-            assert np.array_equal(got, want[b:b + c])
+            assert np.array_equal(got, want[order[b:b + c]])
+
+
+def test_locality_order_cuts_fewer_edges():
+    """partition.locality_order keeps the reference's contract (equal contiguous blocks of axis 0, PY:77-79) and only
+    reorders the tiles: 24 tiles on 8 devices -> the three tiles around each cube vertex (24 of 48 tile edges cross
+    devices, 36 in block order; at most 3 neighbour devices), on 4 devices 16 instead of 26."""
+    ident = np.arange(24)
+    assert partition.cut_edges(ident, 2, 8) == 36 and partition.cut_edges(ident, 2, 4) == 26
+    o8, o4 = partition.locality_order(2, 8), partition.locality_order(2, 4)
+    for o in (o8, o4):
+        assert sorted(o.tolist()) == list(range(24))
+    assert partition.cut_edges(o8, 2, 8) == 24 and partition.cut_edges(o4, 2, 4) == 16
+    assert np.array_equal(o8, partition.locality_order(2, 8))              # deterministic: every rank computes the same
+    owner = np.empty(24, dtype=int)
+    owner[o8] = np.arange(24) // 3
+    nb = [set() for _ in range(8)]
+    for a, b in partition.tile_adjacency(2):
+        if owner[a] != owner[b]:
+            nb[owner[a]].add(owner[b]), nb[owner[b]].add(owner[a])
+    assert max(len(x) for x in nb) == 3
+    assert len(partition.tile_adjacency(2)) == 48 and len(partition.tile_adjacency(1)) == 12
+    assert np.array_equal(partition.locality_order(1, 1), np.arange(6))
+    with pytest.raises(ValueError):
+        partition.locality_order(1, 4)
 
 
 _GLOO_WORKER = r"""

@@ -248,8 +248,9 @@ def test_tma_ring_kernel_matches_naive(built_library, dtype, tol, name, N, p):
         assert np.linalg.norm(x[:, c, c] - y[:, c, c]) <= tol * np.linalg.norm(y[:, c, c])
 
 
+@pytest.mark.parametrize("tile_map", ["block", "locality"])
 @pytest.mark.parametrize("p,world", [(1, 2), (2, 4), (2, 8), (1, 6)])
-def test_sharded_contexts_emulated_on_one_gpu(built_library, p, world):
+def test_sharded_contexts_emulated_on_one_gpu(built_library, p, world, tile_map):
     """The multi-rank path with every rank's context on the same GPU: rim / inner split stage, local
     halo fill, C++ exchange plan, pack -> (copy in place of the all-to-all) -> unpack.  Must agree with
     the single-context step and with the NumPy exchange plan."""
@@ -262,16 +263,20 @@ def test_sharded_contexts_emulated_on_one_gpu(built_library, p, world):
     tiles = [orc.faces_to_tiles(x, p, g) for x in ref]
     hs_tiles = orc.faces_to_tiles(par.hs, p, g)
     ranges = partition.block_ranges(6 * p * p, world)
+    # which tile sits at which position of the sharded axis: the reference's order or compact blocks
+    order = np.arange(6 * p * p) if tile_map == "block" else partition.locality_order(p, world)
     ctxs, state, qa, qb, sendb, recvb, plans = [], [], [], [], [], [], []
     for r, (b, c) in enumerate(ranges):
-        ctx = api.Context(N, tiles_per_edge=p, halo=g, axis=case.axis, tangents=orc.centre_tangents(N), tile_begin=b, tile_count=c)
+        ctx = api.Context(N, tiles_per_edge=p, halo=g, axis=case.axis, tangents=orc.centre_tangents(N), tile_begin=b, tile_count=c,
+                          tile_order=order)
+        assert ctx.tiles.tolist() == order[b:b + c].tolist()
         send, recv = ctx.halo_plan([x for x, _ in ranges], [x for _, x in ranges])
-        ref_plan = partition.ExchangePlan(N, p, g, r, ranges)
+        ref_plan = partition.ExchangePlan(N, p, g, r, ranges, order)
         assert send == ref_plan.send_counts and recv == ref_plan.recv_counts
-        ctx.set_topography(torch.from_numpy(np.ascontiguousarray(hs_tiles[b:b + c])).cuda())   # ghosts already filled
+        ctx.set_topography(torch.from_numpy(np.ascontiguousarray(hs_tiles[order[b:b + c]])).cuda())   # ghosts already filled
         ctxs.append(ctx)
         plans.append((send, recv))
-        state.append([torch.from_numpy(np.ascontiguousarray(x[b:b + c])).cuda() for x in tiles])
+        state.append([torch.from_numpy(np.ascontiguousarray(x[order[b:b + c]])).cuda() for x in tiles])
         qa.append([ctx.new_field() for _ in range(3)])
         qb.append([ctx.new_field() for _ in range(3)])
         sendb.append(torch.zeros(max(1, 3 * sum(send)), dtype=torch.float64, device="cuda"))
@@ -306,7 +311,7 @@ def test_sharded_contexts_emulated_on_one_gpu(built_library, p, world):
     n = N // p
     for r, (b, c) in enumerate(ranges):
         for got, w in zip(state[r], want):
-            a_, w_ = got.cpu().numpy(), w[b:b + c]
+            a_, w_ = got.cpu().numpy(), w[order[b:b + c]]
             assert np.linalg.norm(a_[:, g:g + n, g:g + n] - w_[:, g:g + n, g:g + n]) <= 1e-13 * np.linalg.norm(w_[:, g:g + n, g:g + n])
             # edge ghosts (not the corner blocks of interior tile corners handled by the same table) agree too
             for sl in ((slice(None), slice(g, g + n), slice(None)), (slice(None), slice(None), slice(g, g + n))):

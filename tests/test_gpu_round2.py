@@ -509,3 +509,45 @@ def test_post_push_option_matches_the_fill_kernel(built_library):
     for a, b in zip(dev0, dev1):
         assert float((a - b).abs().max()) <= 1e-13 * float(a.abs().max())
     ctx0.close(), ctx1.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# f2: any order of the tiles along axis 0 (cs_config.tile_order)
+# ---------------------------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_tile_order_is_only_a_relabelling(built_library, dtype):
+    """A whole-sphere context whose axis 0 holds the tiles in a shuffled order: ghost fill, three steps, their sums and
+    the diffusion demo give, tile for tile, the bits of the context with the plain order."""
+    N, p, g = 48, 2, 2
+    order = np.random.default_rng(5).permutation(6 * p * p).astype(np.int32)
+    case, par, ref, ctx0, dev0 = _setup("tc5", N, p, dtype)
+    ctx1 = api.Context(N, tiles_per_edge=p, halo=g, dtype=dtype, axis=case.axis, tangents=orc.centre_tangents(N), tile_order=order)
+    perm = torch.from_numpy(order.astype(np.int64)).cuda()
+    dev1 = [x[perm].contiguous() for x in dev0]
+    ctx1.set_topography(torch.from_numpy(orc.faces_to_tiles(par.hs, p, g).astype(dtype)[order]).cuda())
+    raw = [x.clone() for x in dev1]
+    n = N // p
+    for x in raw:                                           # poison the ghosts, fill, compare with the plain order's fill
+        y = torch.full_like(x, float("nan"))
+        y[:, g:g + n, g:g + n] = x[:, g:g + n, g:g + n]
+        x.copy_(y)
+    ctx1.halo_fill_state(*raw)
+    assert all(torch.equal(a, b[perm]) for a, b in zip(raw, dev0))
+    dt = cases.stable_dt(case, 0.5)
+    d0 = torch.zeros(2, dtype=torch.float64, device="cuda")
+    d1 = torch.zeros(2, dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        ctx0.step(*dev0, dt, diag=d0)
+        ctx1.step(*dev1, dt, diag=d1)
+    assert all(torch.equal(a, b[perm]) for a, b in zip(dev1, dev0))
+    a, b = d0.cpu().numpy(), d1.cpu().numpy()                # same cells, another summation order
+    assert np.all(np.abs(a - b) <= 1e-13 * np.abs(a))
+    assert np.all(np.abs(ctx1.diagnostics(*dev1).cpu().numpy() - ctx0.diagnostics(*dev0).cpu().numpy()) <= 1e-13 * np.abs(a))
+    t0, t1 = ctx0.new_field(), ctx1.new_field()
+    ctx0.scalar_diffuse(dev0[0], t0, 1e3)
+    ctx1.scalar_diffuse(dev1[0], t1, 1e3)
+    assert torch.equal(t1, t0[perm])
+    with pytest.raises(ValueError):
+        api.Context(N, tiles_per_edge=p, halo=g, tile_order=np.zeros(24, dtype=np.int32))
+    ctx0.close(), ctx1.close()

@@ -18,7 +18,7 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ok = True
-for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "peer"), (96, 2, True, True, "peer"),
+for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "peer"), (96, 2, True, True, "peer"), (96, 2, True, True, "peer-block"),
                                    (96, 2, True, False, "nccl"), (96, 2, "side", True, "peer"), (96, 2, "side", False, "nccl"),
                                    (96, 2, False, False, "peer"), (96, 2, False, True, "nccl")):
     if (6 * p * p) % world:
@@ -28,16 +28,17 @@ for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "pee
     par = orc.Params(N, g, axis=case.axis, hs=case.hs)
     ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
     st = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis, device=local, rank=rank,
-                                world=world, tangents=orc.centre_tangents(N), overlap=overlap, sums_of_entry_state=entry, halo_path=path)
-    if path == "peer" and "peer stores" not in st.halo_path:
+                                world=world, tangents=orc.centre_tangents(N), overlap=overlap, sums_of_entry_state=entry, halo_path=path.split("-")[0],
+                                tile_map="block" if path.endswith("-block") else "locality")
+    if path.startswith("peer") and "peer stores" not in st.halo_path:
         print(f"rank {rank}: the peer path fell back to NCCL ({st.halo_path})", flush=True)
         ok = False
     b, c = st.tile_begin, st.tile_count
     n = N // p
-    raw = [orc.faces_to_tiles(orc.pad(x, g), p, g)[b:b + c] for x in (case.h, case.u1, case.u2)]   # ghosts empty
+    raw = [orc.faces_to_tiles(orc.pad(x, g), p, g)[st.tiles] for x in (case.h, case.u1, case.u2)]   # ghosts empty
     dev = [torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in raw]
     if case.hs is not None:
-        st.set_topography(torch.from_numpy(np.ascontiguousarray(orc.faces_to_tiles(orc.pad(case.hs, g), p, g)[b:b + c])).cuda())
+        st.set_topography(torch.from_numpy(np.ascontiguousarray(orc.faces_to_tiles(orc.pad(case.hs, g), p, g)[st.tiles])).cuda())
     st.halo_fill(*dev)
     dt = cases.stable_dt(case)
     m0 = st.diagnostics(*dev).cpu().numpy()
@@ -48,7 +49,7 @@ for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "pee
         ref = orc.step(par, ref, dt)
     m1 = st.diagnostics(*dev).cpu().numpy()
     mf = fused.cpu().numpy()
-    want = [orc.faces_to_tiles(x, p, g)[b:b + c] for x in ref]
+    want = [orc.faces_to_tiles(x, p, g)[st.tiles] for x in ref]
     errs = []
     for got, w in zip(dev, want):
         a = got.cpu().numpy()
