@@ -27,7 +27,7 @@ def test_sharded_stepper_under_nccl(built_library, world):
         pytest.skip(f"needs {world} visible GPUs")
     port = 29500 + world + (os.getpid() % 200)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
-           "--master-addr", "127.0.0.1", "--master-port", str(port), str(ROOT / "tools" / "check_sharded.py")]
+           "--master-addr", "127.0.0.1", "--master-port", str(port), str(ROOT / "tests" / "multi_gpu_check.py")]
     res = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=900)
     sys.stdout.write(res.stdout[-4000:])
     assert res.returncode == 0, res.stdout[-4000:] + res.stderr[-4000:]
