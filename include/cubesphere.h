@@ -302,6 +302,9 @@ CS_API int cs_halo_peer_alloc(cs_ctx* ctx, void* handles_out, size_t handles_byt
 CS_API int cs_halo_peer_connect(cs_ctx* ctx, int n_peers, int my_rank, const void* all_handles, const int64_t* remote_offsets);
 CS_API int cs_halo_push(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* stream);
 CS_API int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields, void* stream);
+/* How many times a pull gave up waiting for a peer's flag (about two seconds each; the ghosts of that fill are then stale).
+ * Non-zero means the ranks' fills fell out of step or a peer died.  Synchronises with the device. */
+CS_API int cs_halo_peer_timeouts(cs_ctx* ctx, unsigned int* count_host);
 
 /*
  * Split stage for overlap on shards: part = 0 computes cells that need no remote

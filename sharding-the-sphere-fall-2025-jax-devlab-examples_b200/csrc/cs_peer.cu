@@ -41,7 +41,7 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
     return v;
 }
 
-// counters (device, own): [0] pushes done, [1] pulls done, [2] push ticket, [3] pull ticket
+// counters (device, own): [0] pushes done, [1] pulls done, [2] push ticket, [3] pull ticket, [4] waits that timed out
 template <typename R>
 __global__ void __launch_bounds__(PEER_THREADS)
 halo_push_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restrict__ v, const int32_t* __restrict__ src,
@@ -87,7 +87,17 @@ halo_pull_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const 
         for (int r = 0; r < n_peers; ++r) {
             if (r == me || peer_off[r + 1] == peer_off[r]) continue;
             const unsigned int* f = flags + parity * n_peers + r;
-            while ((int)(ld_acquire_sys(f) - epoch) < 0) __nanosleep(64);     // epochs wrap: compare as a signed difference
+            // epochs wrap: compare as a signed difference.  A peer that never issues this fill (a rank that died, or a
+            // caller that did not keep the ranks' fills in step) must not hang the GPU: after about two seconds the
+            // wait gives up, counts the event (cs_halo_peer_timeouts) and the scatter goes on with stale data
+            const long long t_start = clock64();
+            while ((int)(ld_acquire_sys(f) - epoch) < 0) {
+                __nanosleep(64);
+                if (clock64() - t_start > 4000000000LL) {
+                    atomicAdd(&counters[4], 1u);
+                    break;
+                }
+            }
         }
     }
     __syncthreads();
@@ -149,7 +159,7 @@ extern "C" int cs_halo_peer_alloc(cs_ctx* ctx, void* handles_out, size_t handles
     ctx->peer = P;
     P->n_peers = (int)ctx->peers.size();
     const size_t bytes = (size_t)(ctx->recv_total > 0 ? ctx->recv_total : 1) * 3 * ctx->esize;
-    const size_t fbytes = ((size_t)2 * P->n_peers + 4) * sizeof(unsigned int);
+    const size_t fbytes = ((size_t)2 * P->n_peers + 8) * sizeof(unsigned int);
     if (cudaMalloc(&P->recv[0], bytes) != cudaSuccess || cudaMalloc(&P->recv[1], bytes) != cudaSuccess ||
         cudaMalloc((void**)&P->flags, fbytes) != cudaSuccess)
         return cs_fail(ctx, CS_E_NOMEM, "cs_halo_peer_alloc: cudaMalloc failed");
@@ -242,5 +252,14 @@ extern "C" int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields,
                                                              P->n_peers, P->me, ctx->recv_total, nfields, counters);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
+    return CS_OK;
+}
+
+extern "C" int cs_halo_peer_timeouts(cs_ctx* ctx, unsigned int* count_host) {
+    if (!ctx || !count_host) return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_timeouts: NULL argument");
+    cs_peer_state* P = ctx->peer;
+    if (!P) return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_timeouts: no peer exchange on this context");
+    CS_ON_DEVICE(ctx, ctx->device);
+    CS_CUDA(ctx, cudaMemcpy(count_host, P->flags + 2 * P->n_peers + 4, sizeof(unsigned int), cudaMemcpyDeviceToHost));
     return CS_OK;
 }

@@ -63,6 +63,7 @@ _PROTOTYPES = {
     "cs_halo_unpack": (C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_halo_peer_alloc": (C.c_int, [_VP, _VP, C.c_size_t]),
     "cs_halo_peer_connect": (C.c_int, [_VP, C.c_int, C.c_int, _VP, C.POINTER(C.c_int64)]),
+    "cs_halo_peer_timeouts": (C.c_int, [_VP, C.POINTER(C.c_uint)]),
     "cs_halo_push": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_halo_pull": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_scalar_diffuse": (C.c_int, [_VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP]),

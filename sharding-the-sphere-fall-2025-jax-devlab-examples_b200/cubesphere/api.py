@@ -494,6 +494,12 @@ class Context:
         off = (C.c_int64 * n)(*[int(x) for x in remote_offsets])
         self._check(self._lib.cs_halo_peer_connect(self._h, n, int(my_rank), C.c_char_p(blob), off))
 
+    def halo_peer_timeouts(self):
+        """Number of pulls that gave up waiting for a peer (0 in a healthy run)."""
+        n = C.c_uint(0)
+        self._check(self._lib.cs_halo_peer_timeouts(self._h, C.byref(n)))
+        return int(n.value)
+
     def halo_push(self, h, u, v, nfields=3):
         up = self._ptr(u, "u") if u is not None else None
         vp = self._ptr(v, "v") if v is not None else None

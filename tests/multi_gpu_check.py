@@ -72,6 +72,9 @@ for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "pee
                                                 abs(rec[k, 1] - rec_ref[k][1]) <= 1e-12 * abs(rec_ref[k][1]) for k in range(3))
     ok = ok and good
     print(f"rank {rank}/{world} C{N} p={p} overlap={overlap} entry_sums={entry} halo={path}: max rel err {max(errs):.2e}, mass drift {(m1[0]-m0[0])/m0[0]:.1e} -> {'ok' if good else 'FAIL'}", flush=True)
+    if "peer stores" in st.halo_path and st.ctx.halo_peer_timeouts() != 0:
+        print(f"rank {rank}: a pull timed out waiting for a peer", flush=True)
+        ok = False
     st.close()
 t = torch.tensor([int(ok)], device="cuda")
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
