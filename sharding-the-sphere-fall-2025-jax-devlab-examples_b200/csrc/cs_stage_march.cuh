@@ -524,7 +524,6 @@ __device__ __forceinline__ void march_item(const StageParams<R>& P, const MarchG
     }
     if (J < J1) row(Dc, Dn, J);
 }
-
 // One (mass, energy) partial per slot (a work item, or a warp of the step kernel); the warp that takes the last ticket
 // adds the partials in index order, so the result does not depend on which warp finishes when (no floating-point
 // atomics).  `scale_e`: SUMS == 1 carries twice the energy density, SUMS == 2 the density itself.
