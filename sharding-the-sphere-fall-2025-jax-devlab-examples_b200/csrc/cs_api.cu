@@ -122,12 +122,7 @@ int enqueue_step(cs_ctx* ctx, void* h, void* u, void* v, double dt, double* diag
         // a single-stage scheme has nothing else to read from, so it goes through scratch
         void** dst = (k == ns - 1 && ns > 1) ? q0 : (k % 2 == 0 ? ctx->qa : ctx->qb);
         // the last stage also produces the conservation sums of the new state when its kernel can (K3 fused into K2)
-        // intermediate stages: the stage kernel pushes the edge ghosts itself when it can (corner blocks, which the
-        // stencil never reads, stay stale in the scratch buffers); the last stage is followed by the real fill, so
-        // the state handed back has every ghost cell as cs_halo_fill_state leaves it
-        ctx->want_post_push = (k < ns - 1);
         rc = cs_launch_stage(ctx, q0, cur, dst, pr[k].a, pr[k].b, dt, 2, k == ksum ? diag_out : nullptr, entry, s);
-        ctx->want_post_push = false;
         if (rc) return rc;
         if (k == ksum) diag_fused = ctx->stage_diag_fused;
         if (k == ksum && diag_out && !diag_fused && entry) {

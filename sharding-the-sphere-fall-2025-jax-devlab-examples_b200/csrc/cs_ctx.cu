@@ -40,7 +40,7 @@ extern "C" int cs_ctx_set_option(cs_ctx* ctx, const char* name, int value) {
         {"march_prefetch", &ctx->tune.march_prefetch}, {"march_rows", &ctx->tune.march_rows}, {"march_vec", &ctx->tune.march_vec},
         {"march_unit", &ctx->tune.march_unit},         {"reserve_sms", &ctx->tune.reserve_sms}, {"tma_ring", &ctx->tune.tma_ring},
         {"fused_halo", &ctx->tune.fused_halo},         {"step_graph", &ctx->tune.step_graph},   {"fused_diag", &ctx->tune.fused_diag},
-        {"step_kernel", &ctx->tune.step_kernel},       {"post_push", &ctx->tune.post_push},
+        {"step_kernel", &ctx->tune.step_kernel},
     };
     for (auto& o : opts)
         if (std::strcmp(o.key, name) == 0) {
@@ -241,7 +241,6 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
     tu.fused_diag = env_int("CS_FUSED_DIAG", tu.fused_diag);
     tu.step_kernel = env_int("CS_STEP_KERNEL", tu.step_kernel);
     tu.step_debug = env_int("CS_STEP_DEBUG", tu.step_debug);
-    tu.post_push = env_int("CS_POST_PUSH", tu.post_push);
     *out = ctx;
     return CS_OK;
 }

@@ -45,8 +45,6 @@ struct CsTuning {
     int tma_ring = 6;            // CS_TMA_RING
     int fused_halo = 1;          // CS_FUSED_HALO: 0 vetoes cfg.fused_halo
     int step_graph = 1;          // CS_STEP_GRAPH: 0 = cs_step enqueues its launches instead of replaying a graph
-    int post_push = 0;           // CS_POST_PUSH: 1 = cs_step's intermediate stages push their edge ghosts themselves after the
-                                 // march instead of a fill launch (measured slower: 0.307 vs 0.294 ms per step)
     int step_debug = 0;          // CS_STEP_DEBUG: timing experiments on the step kernel (wrong results)
     int step_kernel = 0;         // CS_STEP_KERNEL: 1 = cs_step uses the one-launch-per-step kernel where it can (measured
                                  // slower than the replayed graph of stage launches at every size: DESIGN.md 4.2)
@@ -99,7 +97,6 @@ struct cs_ctx {
     std::vector<double> x_base;                  // the N centre tangents the context was created with
     int4* d_push = nullptr;                      // [T][4] (dst local tile or -1, dst edge, reverse, code)
     bool push_complete = false;                  // every neighbour tile is local
-    bool want_post_push = false;                 // set by cs_step around its intermediate stages
     bool stage_pushed = false;                   // the last stage launch stored the edge ghosts itself
     bool stage_diag_fused = false;               // the last stage launch wrote its diag_out itself (K3 fused into K2)
     bool pdl = false;                            // programmatic dependent launch for stage / halo kernels (CS_PDL=1: on)

@@ -110,15 +110,8 @@ int launch_rim(cs_ctx* ctx, const StageParams<R>& P, double* diag_out, int sums_
 
 template <typename R, int V, int LIM, int MINB>
 int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* diag_out, int sums_in, cudaStream_t s) {
-    MarchGeom G = march_geometry(ctx, stage_march_kernel<R, V, LIM, MINB, false>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
-    // cs_step asks for the ghosts of an intermediate stage to be pushed by the stage kernel itself (no fill launch)
-    StageParams<R> PP = P;
-    if (ctx->want_post_push && lo == 0 && !P.push && ctx->push_complete && ctx->d_push && !ctx->d_rot && !ctx->d_interp_dst &&
-        ctx->tune.post_push) {
-        G.post_push = 1;
-        PP.push = ctx->d_push;
-        ctx->stage_pushed = true;
-    }
+    const MarchGeom G = march_geometry(ctx, stage_march_kernel<R, V, LIM, MINB, false>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
+    const StageParams<R>& PP = P;
     const int warps = CS_MARCH_THREADS / 32;
     // First stage, (a, b) = (0, 1): a variant compiled without q0 and without the multiplications by b.  11 % fewer
     // instructions in both precisions, but only fp64 gains (169 -> 154 us at C1536); the fp32 build of it is

@@ -59,7 +59,6 @@ MarchGeom march_geometry(cs_ctx* ctx, Kernel kernel, int V, int n, int g, int m,
     MarchGeom G;
     G.xlo = G.ylo = lo, G.xhi = G.yhi = hi;
     G.prefetch = ctx->tune.march_prefetch;
-    G.post_push = 0;
     G.ngroups = m / V;
     G.grp0 = (lo + g) / V;
     const int grp_last = (hi - 1 + g) / V;

@@ -26,7 +26,6 @@ struct MarchGeom {
     int nchunks;              // warps along x
     int nstrips;              // strips along y
     int nitems;               // nchunks * nstrips * tiles (one warp each)
-    int post_push;            // after its march a warp copies its boundary cells into the neighbours' edge ghosts
 };
 
 __device__ __forceinline__ void march_prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -563,9 +562,6 @@ __device__ __forceinline__ void march_finish_sums(const StageParams<R>& P, int s
     }
 }
 
-template <typename R, int V>
-__device__ __forceinline__ void march_push_item(const StageParams<R>& P, const MarchGeom& G, const int item, const int lane);
-
 // One stage per launch: one work item per warp, items flattened chunk-fastest into a 1-D grid, so consecutive warps
 // take neighbouring column chunks of the same strip and no warp slot idles when nchunks % 4 != 0.
 template <typename R, int V, int LIM, int MINB, bool PUSH, bool UNIT = false, int SUMS = 0>
@@ -576,9 +572,9 @@ stage_march_kernel(const __grid_constant__ StageParams<R> P, const __grid_consta
     if (item >= G.nitems) return;                         // whole warp leaves together
     double dmass = 0.0, denergy2 = 0.0;                   // SUMS: this thread's share of the conservation sums
     march_item<R, V, LIM, PUSH, UNIT, SUMS, true>(P, G, item, lane, dmass, denergy2);
-    // ghost fill folded into the stage (intermediate stages of cs_step): the warp that computed boundary cells stores
-    // them into the edge ghosts that mirror them, after its march -- the marching loop itself is untouched
-    if (G.post_push) march_push_item<R, V>(P, G, item, lane);
+    // (A push of the boundary cells into the neighbours' ghosts after the march -- march_push_item, as the step kernel
+    // does -- was tried here as an option for cs_step's intermediate stages: slower when on, and its mere presence in this
+    // kernel, switched off, cost the fp32 step 8 us.  DESIGN.md 4.2.)
     if constexpr (SUMS != 0) march_finish_sums<R>(P, item, G.nitems, lane, dmass, denergy2, SUMS == 1 ? 0.5 : 1.0);
 }
 

@@ -491,26 +491,6 @@ def test_diffusion_demo_matches_the_oracle(built_library, N, p, dtype, tol):
     ctx.close()
 
 
-def test_post_push_option_matches_the_fill_kernel(built_library):
-    """CS_POST_PUSH=1 (opt-in): the intermediate stages of cs_step push their edge ghosts themselves; the step's result
-    and its ghosts are those of the default path to rounding."""
-    case, par, ref, ctx0, dev0 = _setup("tc5", 48, 2, np.float64)
-    os.environ["CS_POST_PUSH"] = "1"
-    try:
-        _, _, _, ctx1, dev1 = _setup("tc5", 48, 2, np.float64)
-    finally:
-        del os.environ["CS_POST_PUSH"]
-    dt = cases.stable_dt(case, 0.5)
-    l0 = ctx1.launches
-    for _ in range(3):
-        ctx0.step(*dev0, dt)
-        ctx1.step(*dev1, dt)
-    assert ctx1.launches - l0 == 3 * 4                       # three stages and ONE ghost fill per step
-    for a, b in zip(dev0, dev1):
-        assert float((a - b).abs().max()) <= 1e-13 * float(a.abs().max())
-    ctx0.close(), ctx1.close()
-
-
 # ---------------------------------------------------------------------------------------------------------------
 # f2: any order of the tiles along axis 0 (cs_config.tile_order)
 # ---------------------------------------------------------------------------------------------------------------
