@@ -170,6 +170,8 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
         ctx->inv[t] = k;
     }
     ctx->cfg.tile_order = nullptr;
+    for (int k = 0; k < T; ++k)
+        if (ctx->order[cfg->tile_begin + k] != cfg->tile_begin + k) ctx->plain_order = false;
     ctx->dtype = cfg->dtype, ctx->esize = esize, ctx->device = cfg->device;
     ctx->field_elems = (size_t)T * m * m;
     ctx->pitch16 = ((size_t)m * esize) % 16 == 0;   // vectorised / TMA stage kernels need it

@@ -62,6 +62,7 @@ struct cs_ctx {
     int T_all = 0, t0 = 0, T = 0;                // t0, T: first POSITION along axis 0 and number of positions owned
     std::vector<int32_t> order, inv;             // position -> tile id (cfg.tile_order or the identity) and its inverse
     int32_t* d_tile_ids = nullptr;               // [T] tile ids of the owned positions
+    bool plain_order = true;                     // ... which are simply t0, t0 + 1, ...: kernels skip the table
     int local_index(int tile) const {            // index of a tile inside this context's shard, or -1
         const int pos = inv[tile];
         return pos >= t0 && pos < t0 + T ? pos - t0 : -1;

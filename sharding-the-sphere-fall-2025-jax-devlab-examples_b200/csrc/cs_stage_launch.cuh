@@ -31,7 +31,8 @@ StageParams<R> make_params(cs_ctx* ctx, const void* const q0[3], const void* con
     P.diag_out = nullptr;
     P.sums_in = 0;
     P.n = ctx->n, P.g = ctx->g, P.m = ctx->m, P.p = ctx->p, P.T = ctx->T;
-    P.tile_ids = ctx->d_tile_ids;
+    P.tile_ids = ctx->plain_order ? nullptr : ctx->d_tile_ids;
+    P.t0 = ctx->t0;
     P.part = part;
     P.advect_only = ctx->cfg.advect_only;
     // a convex pair (a + b == 1) must stay one after rounding to R, or every step leaks a + b - 1 of the

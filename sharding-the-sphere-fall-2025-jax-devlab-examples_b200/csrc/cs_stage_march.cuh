@@ -313,7 +313,7 @@ __device__ __forceinline__ void march_item(const StageParams<R>& P, const MarchG
     const int j0 = G.ylo + strip * G.rows;
     const int j1 = min(j0 + G.rows, G.yhi);
     const int m = P.m, g = P.g;
-    const TileCoord tc = cs_tile_coord(P.tile_ids[t], P.p);
+    const TileCoord tc = cs_tile_coord(cs_tile_id(P, t), P.p);
     const int grp = G.grp0 + chunk * CS_MARCH_OUT_LANES + lane - 1;
     const bool lane_out = lane >= 1 && lane <= CS_MARCH_OUT_LANES && grp < G.ngroups;
     const int col0 = min(max(grp, 0), G.ngroups - 1) * V;

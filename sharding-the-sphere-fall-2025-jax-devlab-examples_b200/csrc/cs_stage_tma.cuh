@@ -101,7 +101,7 @@ stage_tma_kernel(const __grid_constant__ StageParams<R> P, const __grid_constant
     const int j0 = G.ylo + strip * G.rows;
     const int j1 = min(j0 + G.rows, G.yhi);
     const int m = P.m, g = P.g;
-    const TileCoord tc = cs_tile_coord(P.tile_ids[t], P.p);
+    const TileCoord tc = cs_tile_coord(cs_tile_id(P, t), P.p);
     const int gs = G.grp0 + chunk * CS_MARCH_OUT_LANES - 1;             // column group of lane 0 (may be -1)
     const int grp = gs + lane;
     const bool lane_out = lane >= 1 && lane <= CS_MARCH_OUT_LANES && grp < G.ngroups;
