@@ -14,6 +14,10 @@ definitions shows up as a diff against committed data rather than going unnotice
   step_tc2_c16.npz  Williamson case 2 (alpha = pi/4), C16: state after 5 SSP-RK3 / MC steps, mass, energy
   step_tc5_c16.npz  Williamson case 5 (mountain), C16: the same, with the topography
   step_tc1_c16.npz  Williamson case 1 (advection only, alpha = pi/4), C16, SSP-RK2 / minmod
+  diffuse_c12.npz   (round 2) the heat-diffusion demo: checkerboard source on face 0, C12, field after 30 steps
+  interp_c12.npz    (round 2) random (h, u, v) on C12 with the edge ghosts built by 1-D interpolation + rotation
+                    (oracle/seam_study.py, mode "interp"); corner blocks are not part of that construction
+Run with an argument (`python tests/golden/make_golden.py round2`) to write only the round-2 files.
 """
 import json
 import sys
@@ -66,12 +70,42 @@ def step_fixture(name, case_name, N, nsteps, rk, limiter, **kw):
                         h1=out[0], u1=out[1], v1=out[2], diag0=np.asarray(d0), diag1=np.asarray(d1))
 
 
+def diffuse_fixture(name, N, nsteps):
+    g = 2
+    par = orc.Params(N, g)
+    src = orc.checkerboard_source(N, g)
+    c = slice(g, g + N)
+    kdt = 0.2 * par.delta ** 2 / max(par.gi11[c, c].max(), par.gi22[c, c].max())
+    T = np.zeros_like(src)
+    for _ in range(nsteps):
+        T = orc.diffuse(par, T, kdt, src, 1.0)
+    np.savez_compressed(HERE / name, N=N, g=g, nsteps=nsteps, kdt=kdt, source=src, T=T)
+
+
+def interp_fixture(name, N):
+    from oracle import seam_study
+    g = 2
+    rng = np.random.default_rng(20251118)
+    M = N + 2 * g
+    h, u, v = (rng.standard_normal((6, M, M)) for _ in range(3))
+    halo = seam_study.SeamHalo(N, g, "interp")
+    ho, uo, vo = halo(h.copy(), u.copy(), v.copy())
+    np.savez_compressed(HERE / name, N=N, g=g, h_in=h, u_in=u, v_in=v, h_out=ho, u_out=uo, v_out=vo, dst=halo.dst,
+                        tangents=halo.tangents)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "round2":
+        diffuse_fixture("diffuse_c12.npz", 12, 30)
+        interp_fixture("interp_c12.npz", 12)
+        sys.exit(0)
     (HERE / "reference_schedule.json").write_text(json.dumps(REFERENCE_SCHEDULE) + "\n")
     halo_fixture("halo_c8_g2.npz", 8, 2, 1)
     halo_fixture("halo_c12_p2.npz", 12, 2, 2)
     step_fixture("step_tc2_c16.npz", "tc2", 16, 5, "ssprk3", "mc", alpha0=np.pi / 4)
     step_fixture("step_tc5_c16.npz", "tc5", 16, 5, "ssprk3", "mc")
     step_fixture("step_tc1_c16.npz", "tc1", 16, 5, "ssprk2", "minmod", alpha0=np.pi / 4)
+    diffuse_fixture("diffuse_c12.npz", 12, 30)
+    interp_fixture("interp_c12.npz", 12)
     for f in sorted(HERE.glob("*.npz")):
         print(f.name, f.stat().st_size, "bytes")
