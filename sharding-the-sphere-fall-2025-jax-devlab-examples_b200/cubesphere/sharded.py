@@ -1,19 +1,21 @@
-"""One-process-per-GPU driver of the step over a block partition of the tiles.
+"""One-process-per-GPU driver of the step over a block partition of the tile axis.
 
 world == 1: every tile lives on one device and the whole step is ``cs_step`` (halo included).
-world  > 1: each rank owns ``6 p^2 / world`` consecutive tiles.  Per RK stage
+world  > 1: each rank owns ``6 p^2 / world`` consecutive POSITIONS of axis 0 (the reference's ``P('tiles')`` block
+partition, JAX-DevLab-Examples.py:40-57, 77-79); which tile sits at which position is ``tile_map`` ("locality": compact
+blocks found by ``partition.locality_order``; "block": tile k at position k).  Per RK stage
 
-    side stream                                          main stream
-    rim cells (what ghosts depend on)  stage kernel, part 1   inner cells: stage kernel, part 0
-    same-rank ghosts                   halo kernel            (almost all of the time)
-    pack boundary cells peers need     one kernel
-    all-to-all                         NCCL over NVLink
-    unpack into remote ghosts          one kernel
-    Inner cells never read ghosts: stage k+1's inner kernel waits for stage k's inner and rim kernels
-    only, the exchange has a whole stage of slack; the streams join at the end of the step.
+    side stream                                                   main stream
+    rim cells (what ghosts depend on)   stage kernel, part 1      inner cells: stage kernel, part 0
+    same-rank ghosts                    ghost-fill kernel         (almost all of the time; leaves the side
+    cross-GPU ghosts, one-sided:        push kernel (stores into   stream a few SMs)
+      the peers' receive buffers over NVLink + flag), pull kernel
+      (waits for its flags, scatters)   -- or, ``halo_path="nccl"``: pack, NCCL all-to-all, unpack
 
-The partition is the reference's: axis 0 block-sharded over a 1-D mesh
-(reference JAX-DevLab-Examples.py:40-57, 77-79).
+Inner cells never read ghosts: stage k+1's inner kernel waits for stage k's inner and rim kernels only, the exchange has
+a whole stage of slack; the streams join at the end of the step, and the whole step is captured into one CUDA graph.
+Conservation sums come out of a stage's two launches (four rank-local doubles) and are combined across ranks either
+every step (``diag=tensor``) or once per read of an on-device record (``diag="history"``, :meth:`read_sums`).
 """
 from __future__ import annotations
 
