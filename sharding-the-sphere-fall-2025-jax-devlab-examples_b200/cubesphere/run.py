@@ -2,6 +2,8 @@
 
     python -m cubesphere.run --case tc5 --N 384 --hours 24 --dtype f64 [--restart out.npz]
     python -m cubesphere.run --resume out.npz --hours 24 [--restart out2.npz]      # carry on from a restart file
+    python -m cubesphere.run --case tc2 --N 96 --second-order                      # interpolated ghosts
+    python -m cubesphere.run --demo diffusion --N 96 --steps 2000                  # the reference's heat-diffusion demo
 
 A thin example of the public API (cases -> Context -> step -> diagnostics -> restart file); the hot path is
 entirely inside the C ABI calls.
@@ -25,10 +27,18 @@ def main(argv=None):
     ap.add_argument("--report-every", type=int, default=50)
     ap.add_argument("--restart", default=None, help="write the final state to this .npz file")
     ap.add_argument("--resume", default=None, help="start from this restart file (case, N, dtype are taken from it)")
+    ap.add_argument("--second-order", action="store_true",
+                    help="ghost values interpolated to our own extended grid (second order at the seams; mass drifts at truncation level)")
+    ap.add_argument("--demo", default=None, choices=["diffusion"],
+                    help="diffusion: heat from a checkerboard source on the top panel spreading over the seams (deck slides 12, 17)")
+    ap.add_argument("--steps", type=int, default=1000, help="--demo diffusion: number of explicit steps")
     args = ap.parse_args(argv)
 
     import torch
-    from . import api, cases, io
+    from . import api, cases, geometry, io
+
+    if args.demo == "diffusion":
+        return diffusion_demo(args)
 
     g = 2
     resumed, step0, time0 = None, 0, 0.0
@@ -54,6 +64,8 @@ def main(argv=None):
         h, u, v = padded(case.h), padded(case.u1), padded(case.u2)
     else:
         h, u, v = (torch.from_numpy(np.ascontiguousarray(resumed[k], dtype=ndt)).cuda() for k in ("h", "u", "v"))
+    if args.second_order:
+        ctx.set_halo_interpolation(geometry.seam_interp_tables(args.N, g))
     if case.hs is not None:
         ctx.set_topography(padded(case.hs))
     ctx.halo_fill_state(h, u, v)
@@ -75,6 +87,38 @@ def main(argv=None):
         io.save_state(args.restart, {"h": h, "u": u, "v": v}, N=args.N, halo=g, step=step0 + nsteps,
                       time=time0 + nsteps * dt, case=args.case)
         print(f"state written to {args.restart}")
+    ctx.close()
+
+
+def diffusion_demo(args):
+    """Checkerboard heat source on face 0 for the first half of the run, then free diffusion: prints the heat on every
+    face (the four neighbours of the top panel must receive equal shares) and the total, which the second half conserves."""
+    import torch
+    from . import api, geometry
+    g, N = 2, args.N
+    ctx = api.Context(N, halo=g, dtype=args.dtype)
+    ndt = np.float32 if args.dtype == "f32" else np.float64
+    t = geometry.centre_tangents(N)
+    X, Y = np.meshgrid(t, t, indexing="xy")
+    met = geometry.metric_terms(X, Y)
+    kdt = 0.2 * (0.5 * np.pi / N) ** 2 / max(met["gi11"].max(), met["gi22"].max())
+    src = np.zeros((6, N + 2 * g, N + 2 * g), dtype=ndt)
+    k = (np.arange(N) * 4) // N
+    src[0, g:g + N, g:g + N] = ((k[:, None] + k[None, :]) % 2) == 0
+    dsrc = torch.from_numpy(src).cuda()
+    a, b = ctx.new_field(), ctx.new_field()
+    sg = torch.from_numpy(met["sg"]).cuda()
+
+    def heat(T):
+        return (T[:, g:g + N, g:g + N].double() * sg).sum(dim=(1, 2)).cpu().numpy()
+
+    half = args.steps // 2
+    for it in range(1, args.steps + 1):
+        ctx.scalar_diffuse(a, b, kdt, source=dsrc if it <= half else None, dt_source=1.0)
+        a, b = b, a
+        if it % max(1, args.steps // 10) == 0:
+            q = heat(a)
+            print(f"  step {it:6d}  heat per face (share of total): " + " ".join(f"{x / q.sum():.4f}" for x in q) + f"   total {q.sum():.6e}")
     ctx.close()
 
 

@@ -531,3 +531,19 @@ def test_tile_order_is_only_a_relabelling(built_library, dtype):
     with pytest.raises(ValueError):
         api.Context(N, tiles_per_edge=p, halo=g, tile_order=np.zeros(24, dtype=np.int32))
     ctx0.close(), ctx1.close()
+
+
+def test_cli_diffusion_demo_and_second_order_flag(built_library, capsys):
+    """python -m cubesphere.run --demo diffusion / --second-order: the two user-facing switches of this round."""
+    from cubesphere import run
+    run.main(["--demo", "diffusion", "--N", "24", "--steps", "40"])
+    out = capsys.readouterr().out.strip().splitlines()
+    shares = [float(x) for x in out[-1].split("(share of total):")[1].split("total")[0].split()]
+    assert len(shares) == 6 and abs(sum(shares) - 1.0) < 1e-3
+    assert max(shares[1:5]) - min(shares[1:5]) < 1e-4 and shares[0] > shares[1] > shares[5]
+    totals = [float(l.split("total")[-1]) for l in out if "total" in l]
+    assert abs(totals[-1] - totals[-3]) <= 1e-12 * totals[-1]          # no source in the second half: heat conserved
+    run.main(["--case", "tc2", "--N", "24", "--hours", "2", "--second-order", "--limiter", "none"])
+    out = capsys.readouterr().out
+    drift = float(out.strip().splitlines()[-2].split("mass drift =")[1].split()[0])
+    assert 0 < abs(drift) < 1e-5                                        # truncation-level, not round-off, and small
