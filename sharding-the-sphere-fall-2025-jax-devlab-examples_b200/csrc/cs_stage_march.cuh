@@ -180,14 +180,25 @@ template <typename R, int V>
 __device__ __forceinline__ void march_row_diag(const StageParams<R>& P, const MarchConst<R, V>& K, const RowDerived<R, V>& D,
                                                R Y, const R (&h)[V], const R (&u)[V], const R (&v)[V], const R (&hs)[V],
                                                const bool (&om)[V], double& mass, double& energy2) {
-    const R a2B = P.a2 * (R(1) + Y * Y), a2Y2 = (P.a2 + P.a2) * Y;
+    const R Bq = R(1) + Y * Y, a2B = P.a2 * Bq, a2Y2 = (P.a2 + P.a2) * Y;
     R pm = R(0), pe = R(0);
 #pragma unroll
     for (int c = 0; c < V; ++c) {
         const R quad = K.a2A[c] * (u[c] * u[c]) - (a2Y2 * K.X[c]) * (u[c] * v[c]) + a2B * (v[c] * v[c]);
-        const R k2 = (D.cc[c] * P.ia2) * quad;                                   // 2 K
+        // metric of the output row: kept from its derivation one iteration ago (fp32), or formed again (fp64: eight more
+        // live double registers in a 255-register kernel cost more than the rsqrt -- 219 vs 236 us per launch at C1536;
+        // in fp32 it is the other way round, 112 vs 116)
+        R ccq, sgq;
+        if constexpr (sizeof(R) == 8) {
+            const R rho2 = K.X[c] * K.X[c] + Bq;
+            const R rinv = cs_rsqrt<R>(rho2), r2 = rinv * rinv;
+            ccq = (K.a2A[c] * Bq) * (r2 * r2), sgq = ccq * (rho2 * rinv);
+        } else {
+            ccq = D.cc[c], sgq = D.sg[c];
+        }
+        const R k2 = (ccq * P.ia2) * quad;                                       // 2 K
         const R col = k2 + P.grav * (h[c] + (hs[c] + hs[c]));                    // 2 (K + g h / 2 + g hs)
-        const R w = D.sg[c] * h[c];
+        const R w = sgq * h[c];
         pm += om[c] ? w : R(0);                                                  // halo lanes and ghost columns do not count
         pe += om[c] ? w * col : R(0);
     }
