@@ -70,6 +70,7 @@ def main(argv=None):
         ctx.set_topography(padded(case.hs))
     ctx.halo_fill_state(h, u, v)
     d0 = ctx.diagnostics(h, u, v).cpu().numpy()
+    h_start = h.clone() if args.case == "tc2" else None      # case 2 is steady: the initial state is the exact solution
     print(f"{args.case} C{args.N} {args.dtype}: dt = {dt:.2f} s, {nsteps} steps from step {step0}, "
           f"mass0 = {d0[0]:.6e}, energy0 = {d0[1]:.6e}")
     torch.cuda.synchronize()
@@ -83,6 +84,10 @@ def main(argv=None):
     torch.cuda.synchronize()
     sec = time.perf_counter() - t0
     print(f"{6.0 * args.N ** 2 * nsteps / sec / 1e9:.2f} G cell-updates/s including the diagnostics read-backs")
+    if h_start is not None:
+        c = slice(g, g + args.N)
+        err = float(torch.linalg.norm((h - h_start)[:, c, c].double()) / torch.linalg.norm(h_start[:, c, c].double()))
+        print(f"steady case: relative L2 error of h against the exact solution = {err:.3e}")
     if args.restart:
         io.save_state(args.restart, {"h": h, "u": u, "v": v}, N=args.N, halo=g, step=step0 + nsteps,
                       time=time0 + nsteps * dt, case=args.case)
