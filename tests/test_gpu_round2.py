@@ -547,3 +547,29 @@ def test_cli_diffusion_demo_and_second_order_flag(built_library, capsys):
     out = capsys.readouterr().out
     drift = float(out.strip().splitlines()[-2].split("mass drift =")[1].split()[0])
     assert 0 < abs(drift) < 1e-5                                        # truncation-level, not round-off, and small
+
+
+@pytest.mark.parametrize("rk", ["euler", "ssprk2", "ssprk3"])
+@pytest.mark.parametrize("entry", [False, True])
+def test_step_sums_for_every_scheme(built_library, rk, entry):
+    """The sums come out of the first stage (entry state) or the last one (new state) whatever the number of stages --
+    also for the one-stage scheme, whose only stage is both."""
+    N, g = 32, 2
+    case = cases.make_case("tc5", N)
+    par = orc.Params(N, g, axis=case.axis, rk=rk, hs=case.hs)
+    ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
+    ctx = api.Context(N, halo=g, dtype=np.float64, rk=rk, axis=case.axis, tangents=orc.centre_tangents(N), sums_of_entry_state=entry)
+    ctx.set_topography(torch.from_numpy(par.hs).cuda())
+    dev = [torch.from_numpy(x).cuda() for x in ref]
+    dt = cases.stable_dt(case, 0.2)
+    diag = torch.zeros(2, dtype=torch.float64, device="cuda")
+    for _ in range(3):
+        before = np.array(orc.diagnostics(par, *ref))
+        ctx.step(*dev, dt, diag=diag)
+        ref = orc.step(par, ref, dt)
+        want = before if entry else np.array(orc.diagnostics(par, *ref))
+        got = diag.cpu().numpy()
+        assert abs(got[0] - want[0]) <= 1e-13 * abs(want[0]) and abs(got[1] - want[1]) <= 1e-12 * abs(want[1]), (rk, entry, got, want)
+    c = slice(g, g + N)
+    assert np.linalg.norm(dev[0].cpu().numpy()[:, c, c] - ref[0][:, c, c]) <= 1e-13 * np.linalg.norm(ref[0][:, c, c])
+    ctx.close()
