@@ -14,7 +14,7 @@
  *     exception: the first cs_step for a new (h, u, v, dt, diag_out) combination captures and
  *     instantiates a CUDA graph (creates a stream, allocates graph memory; CS_STEP_GRAPH=0 opts out);
  *   - the set-up calls synchronise the device and/or allocate: cs_ctx_create, cs_ctx_destroy,
- *     cs_halo_set_rotation, cs_halo_set_interp, cs_halo_plan, cs_halo_peer_alloc, cs_halo_peer_connect, and cs_step_host[_batch] (which own their copies);
+ *     cs_halo_set_rotation, cs_halo_set_interp, cs_halo_interp_sharded, cs_halo_plan, cs_halo_peer_alloc, cs_halo_peer_connect, and cs_step_host[_batch] (which own their copies);
  *   - every call runs on the context's device and restores the calling thread's current CUDA
  *     device before it returns;
  *   - return value 0 = success, negative = CS_E_* below; the text of the last
@@ -180,6 +180,21 @@ CS_API int cs_halo_set_interp(cs_ctx* ctx, size_t n_ghost, const int64_t* dst, c
                        const double* rot, const double* tangents);
 
 /*
+ * The same second-order ghosts on a SHARD (tile_count < 6 p^2), with the one-sided exchange.  The four sources of a ghost
+ * cell may live on this context or on peers, so raw cells travel and the receiver interpolates: send_counts[r] /
+ * send_src (concatenated, element offsets into the local shard) = the cells peer r reads, in the order it expects them;
+ * recv_counts[r] = the cells of peer r this context's rows read; rows as in cs_halo_set_interp, except that src addresses
+ * one virtual space -- offsets below the shard's element count are local cells, shard_elems + k is cell k of the receive
+ * buffer (peer blocks in rank order).  cubesphere.partition.InterpExchangePlan derives all of it from the global tables,
+ * consistently on every rank.  Call it in place of cs_halo_plan, then cs_halo_peer_alloc / cs_halo_peer_connect as usual;
+ * afterwards cs_halo_push + cs_halo_pull produce EVERY ghost cell of the shard (cs_halo_fill_* becomes a no-op).
+ * Replaces: nothing in the reference (see cs_halo_set_interp).
+ */
+CS_API int cs_halo_interp_sharded(cs_ctx* ctx, int n_peers, const int64_t* send_counts, const int64_t* send_src,
+                           const int64_t* recv_counts, size_t n_rows, const int64_t* dst, const int64_t* src, const double* w,
+                           const double* rot, const double* tangents);
+
+/*
  * Ghost-cell table of the context, for callers that want to build rotation
  * tables: writes up to cap entries of (dst_offset, src_offset, code) and returns
  * the ghost-cell count in *n_ghost.  Offsets are element offsets into a field of
@@ -300,6 +315,12 @@ CS_API int cs_halo_unpack(cs_ctx* ctx, const void* recvbuf, void* h, void* u, vo
 #define CS_PEER_HANDLE_BYTES 192
 CS_API int cs_halo_peer_alloc(cs_ctx* ctx, void* handles_out, size_t handles_bytes);
 CS_API int cs_halo_peer_connect(cs_ctx* ctx, int n_peers, int my_rank, const void* all_handles, const int64_t* remote_offsets);
+/* The same connection for contexts of ONE process (several devices with peer access enabled, or several contexts on one
+ * device): no IPC handles -- cs_halo_peer_pointers gives the three device pointers of a context's buffers (out3[3]) and
+ * cs_halo_peer_connect_pointers takes everybody's, [n_peers][3] in rank order.  Same rules otherwise. */
+CS_API int cs_halo_peer_pointers(cs_ctx* ctx, void** out3);
+CS_API int cs_halo_peer_connect_pointers(cs_ctx* ctx, int n_peers, int my_rank, void* const* all_pointers,
+                                  const int64_t* remote_offsets);
 CS_API int cs_halo_push(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* stream);
 CS_API int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields, void* stream);
 /* How many times a pull gave up waiting for a peer's flag (about two seconds each; the ghosts of that fill are then stale).

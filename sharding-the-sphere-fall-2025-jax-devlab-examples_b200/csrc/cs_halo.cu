@@ -128,6 +128,7 @@ int grid_for(const cs_ctx* ctx, int64_t count) {
 }  // namespace
 
 int cs_launch_halo(cs_ctx* ctx, void* h, void* u, void* v, int mask, cudaStream_t s) {
+    if (ctx->interp_sharded) return CS_OK;     // every ghost cell of the shard is produced by cs_halo_pull (local sources too)
     if (ctx->d_interp_dst) {
         const dim3 grid(grid_for(ctx, ctx->n_interp)), block(256);
         if (ctx->dtype == CS_F64)
@@ -263,6 +264,84 @@ extern "C" int cs_halo_set_interp(cs_ctx* ctx, size_t n_ghost, const int64_t* ds
     ctx->n_interp = (int64_t)n_ghost;
     if (tangents) {
         for (int I = 0; I < N + 2 * g; ++I) ctx->xt[I] = tangents[I];
+        return cs_upload_metric(ctx);
+    }
+    return CS_OK;
+}
+
+namespace {
+int upload_offsets(cs_ctx* ctx, bool send, int64_t** d_off);
+}
+
+extern "C" int cs_halo_interp_sharded(cs_ctx* ctx, int n_peers, const int64_t* send_counts, const int64_t* send_src,
+                                      const int64_t* recv_counts, size_t n_rows, const int64_t* dst, const int64_t* src, const double* w,
+                                      const double* rot, const double* tangents) {
+    if (!ctx || !send_counts || !recv_counts || !dst || !src || !w || !rot)
+        return cs_fail(ctx, CS_E_INVALID, "cs_halo_interp_sharded: NULL argument");
+    if (n_peers < 1) return cs_fail(ctx, CS_E_INVALID, "cs_halo_interp_sharded: need at least one peer");
+    if (n_rows != ctx->halo.size())
+        return cs_fail(ctx, CS_E_INVALID, "cs_halo_interp_sharded: %zu rows, the context has %zu ghost cells", n_rows, ctx->halo.size());
+    CS_ON_DEVICE(ctx, ctx->device);
+    CS_CUDA(ctx, cudaDeviceSynchronize());
+    cs_drop_graphs(ctx);
+    // the exchange plan: raw cells, peer blocks in rank order
+    ctx->peers.assign(n_peers, PeerPlan());
+    int64_t so = 0, ro = 0;
+    for (int r = 0; r < n_peers; ++r) {
+        if (send_counts[r] < 0 || recv_counts[r] < 0) return cs_fail(ctx, CS_E_INVALID, "cs_halo_interp_sharded: negative count");
+        ctx->peers[r].send_count = send_counts[r], ctx->peers[r].recv_count = recv_counts[r];
+        ctx->peers[r].send_offset = so, ctx->peers[r].recv_offset = ro;
+        so += send_counts[r], ro += recv_counts[r];
+    }
+    ctx->send_total = so, ctx->recv_total = ro;
+    const int64_t elems = (int64_t)ctx->field_elems;
+    if (elems + ro >= 2147483647LL) return cs_fail(ctx, CS_E_UNSUPPORTED, "cs_halo_interp_sharded: shard + receive buffer exceed 32-bit offsets");
+    if (so > 0 && !send_src) return cs_fail(ctx, CS_E_INVALID, "cs_halo_interp_sharded: NULL send list");
+    std::vector<int32_t> ss((size_t)so);
+    for (int64_t k = 0; k < so; ++k) {
+        if (send_src[k] < 0 || send_src[k] >= elems) return cs_fail(ctx, CS_E_INVALID, "cs_halo_interp_sharded: send offset outside the shard");
+        ss[(size_t)k] = (int32_t)send_src[k];
+    }
+    for (void** q : {(void**)&ctx->d_send_src, (void**)&ctx->d_interp_dst, (void**)&ctx->d_interp_src, &ctx->d_interp_w, &ctx->d_interp_rot})
+        if (*q) cudaFree(*q), *q = nullptr;
+    if (so > 0) {
+        if (cudaMalloc((void**)&ctx->d_send_src, (size_t)so * sizeof(int32_t)) != cudaSuccess)
+            return cs_fail(ctx, CS_E_NOMEM, "cs_halo_interp_sharded: cudaMalloc failed");
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_send_src, ss.data(), (size_t)so * sizeof(int32_t), cudaMemcpyHostToDevice));
+    }
+    int rc;
+    if ((rc = upload_offsets(ctx, true, &ctx->d_send_off))) return rc;
+    if ((rc = upload_offsets(ctx, false, &ctx->d_recv_off))) return rc;
+    // the rows
+    std::vector<int32_t> d32(n_rows);
+    std::vector<int4> s4(n_rows);
+    for (size_t k = 0; k < n_rows; ++k) {
+        const int64_t* q = src + 4 * k;
+        if (dst[k] < 0 || dst[k] >= elems) return cs_fail(ctx, CS_E_INVALID, "cs_halo_interp_sharded: row %zu writes outside the shard", k);
+        for (int j = 0; j < 4; ++j)
+            if (q[j] < 0 || q[j] >= elems + ro) return cs_fail(ctx, CS_E_INVALID, "cs_halo_interp_sharded: row %zu reads outside shard + receive buffer", k);
+        d32[k] = (int32_t)dst[k];
+        s4[k] = make_int4((int)q[0], (int)q[1], (int)q[2], (int)q[3]);
+    }
+    const size_t count = n_rows * 4;
+    if (cudaMalloc((void**)&ctx->d_interp_dst, n_rows * sizeof(int32_t)) != cudaSuccess ||
+        cudaMalloc((void**)&ctx->d_interp_src, n_rows * sizeof(int4)) != cudaSuccess ||
+        cudaMalloc(&ctx->d_interp_w, count * ctx->esize) != cudaSuccess || cudaMalloc(&ctx->d_interp_rot, count * ctx->esize) != cudaSuccess)
+        return cs_fail(ctx, CS_E_NOMEM, "cs_halo_interp_sharded: cudaMalloc failed");
+    CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_dst, d32.data(), n_rows * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_src, s4.data(), n_rows * sizeof(int4), cudaMemcpyHostToDevice));
+    if (ctx->dtype == CS_F64) {
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_w, w, count * 8, cudaMemcpyHostToDevice));
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_rot, rot, count * 8, cudaMemcpyHostToDevice));
+    } else {
+        std::vector<float> tw(w, w + count), tr(rot, rot + count);
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_w, tw.data(), count * 4, cudaMemcpyHostToDevice));
+        CS_CUDA(ctx, cudaMemcpy(ctx->d_interp_rot, tr.data(), count * 4, cudaMemcpyHostToDevice));
+    }
+    ctx->n_interp = (int64_t)n_rows;
+    ctx->interp_sharded = true;
+    if (tangents) {
+        for (int I = 0; I < ctx->N + 2 * ctx->g; ++I) ctx->xt[I] = tangents[I];
         return cs_upload_metric(ctx);
     }
     return CS_OK;

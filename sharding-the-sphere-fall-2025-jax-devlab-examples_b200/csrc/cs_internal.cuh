@@ -95,6 +95,7 @@ struct cs_ctx {
     int4* d_interp_src = nullptr;                // [n_interp] four source offsets
     void* d_interp_w = nullptr;                  // [n_interp][4] weights (state dtype)
     void* d_interp_rot = nullptr;                // [n_interp][4] row-major 2 x 2 (state dtype)
+    bool interp_sharded = false;                 // ... on a shard: sources may be cells of the receive buffer (cs_halo_interp_sharded)
     std::vector<double> x_base;                  // the N centre tangents the context was created with
     int4* d_push = nullptr;                      // [T][4] (dst local tile or -1, dst edge, reverse, code)
     bool push_complete = false;                  // every neighbour tile is local

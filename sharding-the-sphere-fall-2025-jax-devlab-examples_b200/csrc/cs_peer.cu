@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(PEER_THREADS)
 halo_push_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __restrict__ v, const int32_t* __restrict__ src,
                  void* const* __restrict__ peer_recv, unsigned int* const* __restrict__ peer_flags,
                  const int64_t* __restrict__ peer_off, const int64_t* __restrict__ remote_off, int n_peers, int me, int64_t count,
-                 int nfields, unsigned int* counters) {
+                 int nfields, int aos, unsigned int* counters) {
     const unsigned int epoch = counters[0] + 1u;          // written only by the last block of the previous push
     const int parity = (int)(epoch & 1u);
     for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < count; k += (int64_t)gridDim.x * blockDim.x) {
@@ -55,12 +55,18 @@ halo_push_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __re
         while (r + 1 < n_peers && k >= peer_off[r + 1]) ++r;
         const int64_t cnt = peer_off[r + 1] - peer_off[r];
         R* buf = static_cast<R*>(peer_recv[parity * n_peers + r]);       // the PEER's memory
-        const int64_t base = remote_off[r] * nfields + (k - peer_off[r]);
         const int32_t s = src[k];
-        buf[base] = h[s];
-        if (nfields == 3) {
-            buf[base + cnt] = u[s];
-            buf[base + 2 * cnt] = v[s];
+        if (aos) {                                        // [cell][field]: the receiver interpolates raw cells (second-order ghosts)
+            const int64_t base = (remote_off[r] + (k - peer_off[r])) * nfields;
+            buf[base] = h[s];
+            if (nfields == 3) buf[base + 1] = u[s], buf[base + 2] = v[s];
+        } else {                                          // per source rank [field][cell]
+            const int64_t base = remote_off[r] * nfields + (k - peer_off[r]);
+            buf[base] = h[s];
+            if (nfields == 3) {
+                buf[base + cnt] = u[s];
+                buf[base + 2 * cnt] = v[s];
+            }
         }
     }
     __syncthreads();
@@ -76,20 +82,13 @@ halo_push_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __re
     }
 }
 
-template <typename R>
-__global__ void __launch_bounds__(PEER_THREADS)
-halo_pull_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const int32_t* __restrict__ dst,
-                 const uint8_t* __restrict__ code, const R* recv0, const R* recv1, const unsigned int* flags,
-                 const int64_t* __restrict__ peer_off, int n_peers, int me, int64_t count, int nfields, unsigned int* counters) {
-    const unsigned int epoch = counters[1] + 1u;
-    const int parity = (int)(epoch & 1u);
+// Wait (thread 0 of every block) until every source rank's flag for this fill has arrived.
+__device__ __forceinline__ void wait_for_peers(const unsigned int* flags, const int64_t* peer_off, int n_peers, int me, int parity,
+                                               unsigned int epoch, unsigned int* counters) {
     if (threadIdx.x == 0) {
         for (int r = 0; r < n_peers; ++r) {
             if (r == me || peer_off[r + 1] == peer_off[r]) continue;
             const unsigned int* f = flags + parity * n_peers + r;
-            // epochs wrap: compare as a signed difference.  A peer that never issues this fill (a rank that died, or a
-            // caller that did not keep the ranks' fills in step) must not hang the GPU: after about two seconds the
-            // wait gives up, counts the event (cs_halo_peer_timeouts) and the scatter goes on with stale data
             const long long t_start = clock64();
             while ((int)(ld_acquire_sys(f) - epoch) < 0) {
                 __nanosleep(64);
@@ -101,6 +100,63 @@ halo_pull_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const 
         }
     }
     __syncthreads();
+}
+
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+
+// Second-order ghosts on a shard: every ghost cell = ((w0 s0 + w1 s1) + w2 s2) + w3 s3 (then the 2 x 2 for vectors), the
+// sources addressed in one virtual space -- offsets below field_elems are cells of the local shard, field_elems + k is
+// cell k of the receive buffer ([cell][field], what the peers' pushes wrote).  Same rounding as halo_interp_kernel.
+template <typename R>
+__global__ void __launch_bounds__(PEER_THREADS)
+halo_interp_pull_kernel(R* h, R* u, R* v, const int32_t* __restrict__ dst, const int4* __restrict__ src, const R* __restrict__ w,
+                        const R* __restrict__ rot, const R* recv0, const R* recv1, const unsigned int* flags,
+                        const int64_t* __restrict__ peer_off, int n_peers, int me, int64_t rows, int field_elems, int nfields,
+                        unsigned int* counters) {
+    const unsigned int epoch = counters[1] + 1u;
+    const int parity = (int)(epoch & 1u);
+    wait_for_peers(flags, peer_off, n_peers, me, parity, epoch, counters);
+    const R* recv = parity ? recv1 : recv0;
+    auto get = [&](const R* f, int fi, int o) -> R {
+        return o < field_elems ? f[o] : __ldcg(recv + (size_t)(o - field_elems) * nfields + fi);
+    };
+    auto interp = [&](const R* f, int fi, const int4 s, R w0, R w1, R w2, R w3) -> R {
+        return add_rn(add_rn(add_rn(mul_rn(w0, get(f, fi, s.x)), mul_rn(w1, get(f, fi, s.y))), mul_rn(w2, get(f, fi, s.z))),
+                      mul_rn(w3, get(f, fi, s.w)));
+    };
+    for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < rows; k += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t d = dst[k];
+        const int4 s = src[k];
+        const R w0 = w[4 * k], w1 = w[4 * k + 1], w2 = w[4 * k + 2], w3 = w[4 * k + 3];
+        h[d] = interp(h, 0, s, w0, w1, w2, w3);
+        if (nfields == 3) {
+            const R a = interp(u, 1, s, w0, w1, w2, w3), b = interp(v, 2, s, w0, w1, w2, w3);
+            const R* r = rot + 4 * k;
+            u[d] = add_rn(mul_rn(r[0], a), mul_rn(r[1], b));
+            v[d] = add_rn(mul_rn(r[2], a), mul_rn(r[3], b));
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && atomicAdd(&counters[3], 1u) == gridDim.x - 1) {
+        counters[3] = 0;
+        counters[1] = epoch;
+    }
+}
+
+template <typename R>
+__global__ void __launch_bounds__(PEER_THREADS)
+halo_pull_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const int32_t* __restrict__ dst,
+                 const uint8_t* __restrict__ code, const R* recv0, const R* recv1, const unsigned int* flags,
+                 const int64_t* __restrict__ peer_off, int n_peers, int me, int64_t count, int nfields, unsigned int* counters) {
+    const unsigned int epoch = counters[1] + 1u;
+    const int parity = (int)(epoch & 1u);
+    // epochs wrap: compared as a signed difference.  A peer that never issues this fill (a rank that died, or a caller
+    // that did not keep the ranks' fills in step) must not hang the GPU: after about two seconds the wait gives up,
+    // counts the event (cs_halo_peer_timeouts) and the scatter goes on with stale data
+    wait_for_peers(flags, peer_off, n_peers, me, parity, epoch, counters);
     const R* buf = parity ? recv1 : recv0;
     for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < count; k += (int64_t)gridDim.x * blockDim.x) {
         int r = 0;
@@ -172,6 +228,27 @@ extern "C" int cs_halo_peer_alloc(cs_ctx* ctx, void* handles_out, size_t handles
     return CS_OK;
 }
 
+namespace {
+// upload the peers' buffer addresses (as this device sees them) and the offsets of this rank's blocks in their buffers
+int peer_finish(cs_ctx* ctx, cs_peer_state* P, int n_peers, int my_rank, const std::vector<void*>& recv, const std::vector<unsigned int*>& flags,
+                const int64_t* remote_offsets) {
+    P->me = my_rank;
+    std::vector<int64_t> off(remote_offsets, remote_offsets + n_peers);
+    for (void* q : {(void*)P->d_peer_recv, (void*)P->d_peer_flags, (void*)P->d_remote_off})
+        if (q) cudaFree(q);
+    P->d_peer_recv = nullptr, P->d_peer_flags = nullptr, P->d_remote_off = nullptr;
+    if (cudaMalloc((void**)&P->d_peer_recv, recv.size() * sizeof(void*)) != cudaSuccess ||
+        cudaMalloc((void**)&P->d_peer_flags, flags.size() * sizeof(unsigned int*)) != cudaSuccess ||
+        cudaMalloc((void**)&P->d_remote_off, off.size() * sizeof(int64_t)) != cudaSuccess)
+        return cs_fail(ctx, CS_E_NOMEM, "cs_halo_peer_connect: cudaMalloc failed");
+    CS_CUDA(ctx, cudaMemcpy(P->d_peer_recv, recv.data(), recv.size() * sizeof(void*), cudaMemcpyHostToDevice));
+    CS_CUDA(ctx, cudaMemcpy(P->d_peer_flags, flags.data(), flags.size() * sizeof(unsigned int*), cudaMemcpyHostToDevice));
+    CS_CUDA(ctx, cudaMemcpy(P->d_remote_off, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+    P->connected = true;
+    return CS_OK;
+}
+}  // namespace
+
 extern "C" int cs_halo_peer_connect(cs_ctx* ctx, int n_peers, int my_rank, const void* all_handles, const int64_t* remote_offsets) {
     if (!ctx || !all_handles || !remote_offsets) return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_connect: NULL argument");
     cs_peer_state* P = ctx->peer;
@@ -179,7 +256,6 @@ extern "C" int cs_halo_peer_connect(cs_ctx* ctx, int n_peers, int my_rank, const
     if (n_peers != P->n_peers || my_rank < 0 || my_rank >= n_peers)
         return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_connect: %d peers / rank %d do not match the plan (%d peers)", n_peers, my_rank, P->n_peers);
     CS_ON_DEVICE(ctx, ctx->device);
-    P->me = my_rank;
     std::vector<void*> recv(2 * (size_t)n_peers, nullptr);
     std::vector<unsigned int*> flags(n_peers, nullptr);
     const cudaIpcMemHandle_t* hd = static_cast<const cudaIpcMemHandle_t*>(all_handles);
@@ -199,16 +275,32 @@ extern "C" int cs_halo_peer_connect(cs_ctx* ctx, int n_peers, int my_rank, const
         }
         recv[r] = q[0], recv[n_peers + r] = q[1], flags[r] = static_cast<unsigned int*>(q[2]);
     }
-    std::vector<int64_t> off(remote_offsets, remote_offsets + n_peers);
-    if (cudaMalloc((void**)&P->d_peer_recv, recv.size() * sizeof(void*)) != cudaSuccess ||
-        cudaMalloc((void**)&P->d_peer_flags, flags.size() * sizeof(unsigned int*)) != cudaSuccess ||
-        cudaMalloc((void**)&P->d_remote_off, off.size() * sizeof(int64_t)) != cudaSuccess)
-        return cs_fail(ctx, CS_E_NOMEM, "cs_halo_peer_connect: cudaMalloc failed");
-    CS_CUDA(ctx, cudaMemcpy(P->d_peer_recv, recv.data(), recv.size() * sizeof(void*), cudaMemcpyHostToDevice));
-    CS_CUDA(ctx, cudaMemcpy(P->d_peer_flags, flags.data(), flags.size() * sizeof(unsigned int*), cudaMemcpyHostToDevice));
-    CS_CUDA(ctx, cudaMemcpy(P->d_remote_off, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
-    P->connected = true;
+    return peer_finish(ctx, P, n_peers, my_rank, recv, flags, remote_offsets);
+}
+
+extern "C" int cs_halo_peer_pointers(cs_ctx* ctx, void** out3) {
+    if (!ctx || !out3) return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_pointers: NULL argument");
+    cs_peer_state* P = ctx->peer;
+    if (!P) return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_pointers: call cs_halo_peer_alloc first");
+    out3[0] = P->recv[0], out3[1] = P->recv[1], out3[2] = P->flags;
     return CS_OK;
+}
+
+extern "C" int cs_halo_peer_connect_pointers(cs_ctx* ctx, int n_peers, int my_rank, void* const* all_pointers, const int64_t* remote_offsets) {
+    if (!ctx || !all_pointers || !remote_offsets) return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_connect_pointers: NULL argument");
+    cs_peer_state* P = ctx->peer;
+    if (!P) return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_connect_pointers: call cs_halo_peer_alloc first");
+    if (n_peers != P->n_peers || my_rank < 0 || my_rank >= n_peers)
+        return cs_fail(ctx, CS_E_INVALID, "cs_halo_peer_connect_pointers: %d peers / rank %d do not match the plan (%d peers)", n_peers, my_rank,
+                       P->n_peers);
+    CS_ON_DEVICE(ctx, ctx->device);
+    std::vector<void*> recv(2 * (size_t)n_peers, nullptr);
+    std::vector<unsigned int*> flags(n_peers, nullptr);
+    for (int r = 0; r < n_peers; ++r) {
+        recv[r] = all_pointers[3 * r], recv[n_peers + r] = all_pointers[3 * r + 1];
+        flags[r] = static_cast<unsigned int*>(all_pointers[3 * r + 2]);
+    }
+    return peer_finish(ctx, P, n_peers, my_rank, recv, flags, remote_offsets);
 }
 
 extern "C" int cs_halo_push(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* stream) {
@@ -223,11 +315,11 @@ extern "C" int cs_halo_push(cs_ctx* ctx, const void* h, const void* u, const voi
     if (ctx->dtype == CS_F64)
         halo_push_kernel<double><<<grid, PEER_THREADS, 0, s>>>((const double*)h, (const double*)u, (const double*)v, ctx->d_send_src,
                                                               P->d_peer_recv, P->d_peer_flags, ctx->d_send_off, P->d_remote_off, P->n_peers,
-                                                              P->me, ctx->send_total, nfields, counters);
+                                                              P->me, ctx->send_total, nfields, ctx->interp_sharded ? 1 : 0, counters);
     else
         halo_push_kernel<float><<<grid, PEER_THREADS, 0, s>>>((const float*)h, (const float*)u, (const float*)v, ctx->d_send_src,
                                                              P->d_peer_recv, P->d_peer_flags, ctx->d_send_off, P->d_remote_off, P->n_peers,
-                                                             P->me, ctx->send_total, nfields, counters);
+                                                             P->me, ctx->send_total, nfields, ctx->interp_sharded ? 1 : 0, counters);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;
@@ -241,6 +333,24 @@ extern "C" int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields,
     CS_ON_DEVICE(ctx, ctx->device);
     cudaStream_t s = (cudaStream_t)stream;
     unsigned int* counters = P->flags + 2 * P->n_peers;
+    if (ctx->interp_sharded) {
+        const int grid = grid_for(ctx, ctx->n_interp);
+        if (ctx->dtype == CS_F64)
+            halo_interp_pull_kernel<double><<<grid, PEER_THREADS, 0, s>>>((double*)h, (double*)u, (double*)v, ctx->d_interp_dst, ctx->d_interp_src,
+                                                                         (const double*)ctx->d_interp_w, (const double*)ctx->d_interp_rot,
+                                                                         (const double*)P->recv[0], (const double*)P->recv[1], P->flags,
+                                                                         ctx->d_recv_off, P->n_peers, P->me, ctx->n_interp,
+                                                                         (int)ctx->field_elems, nfields, counters);
+        else
+            halo_interp_pull_kernel<float><<<grid, PEER_THREADS, 0, s>>>((float*)h, (float*)u, (float*)v, ctx->d_interp_dst, ctx->d_interp_src,
+                                                                        (const float*)ctx->d_interp_w, (const float*)ctx->d_interp_rot,
+                                                                        (const float*)P->recv[0], (const float*)P->recv[1], P->flags,
+                                                                        ctx->d_recv_off, P->n_peers, P->me, ctx->n_interp,
+                                                                        (int)ctx->field_elems, nfields, counters);
+        ctx->launches++;
+        CS_CUDA(ctx, cudaGetLastError());
+        return CS_OK;
+    }
     const int grid = grid_for(ctx, ctx->recv_total);
     if (ctx->dtype == CS_F64)
         halo_pull_kernel<double><<<grid, PEER_THREADS, 0, s>>>((double*)h, (double*)u, (double*)v, ctx->d_recv_dst, ctx->d_recv_code,

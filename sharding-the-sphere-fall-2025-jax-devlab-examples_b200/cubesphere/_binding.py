@@ -46,6 +46,9 @@ _PROTOTYPES = {
     "cs_halo_set_rotation": (C.c_int, [_VP, C.POINTER(C.c_double), C.c_size_t]),
     "cs_halo_set_interp": (C.c_int, [_VP, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_double),
                                      C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "cs_halo_interp_sharded": (C.c_int, [_VP, C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_size_t,
+                                         C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                         C.POINTER(C.c_double)]),
     "cs_halo_table_info": (C.c_int, [_VP, C.c_size_t, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                      C.POINTER(C.c_int32), C.POINTER(C.c_size_t)]),
     "cs_set_topography": (C.c_int, [_VP, _VP, _VP]),
@@ -63,6 +66,8 @@ _PROTOTYPES = {
     "cs_halo_unpack": (C.c_int, [_VP, _VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_halo_peer_alloc": (C.c_int, [_VP, _VP, C.c_size_t]),
     "cs_halo_peer_connect": (C.c_int, [_VP, C.c_int, C.c_int, _VP, C.POINTER(C.c_int64)]),
+    "cs_halo_peer_pointers": (C.c_int, [_VP, C.POINTER(_VP)]),
+    "cs_halo_peer_connect_pointers": (C.c_int, [_VP, C.c_int, C.c_int, C.POINTER(_VP), C.POINTER(C.c_int64)]),
     "cs_halo_peer_timeouts": (C.c_int, [_VP, C.POINTER(C.c_uint)]),
     "cs_halo_push": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP]),
     "cs_halo_pull": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, _VP]),

@@ -376,6 +376,23 @@ class Context:
         self._check(self._lib.cs_halo_set_interp(self._h, dst.shape[0], dst.ctypes.data_as(i64), src.ctypes.data_as(i64),
                                                  w.ctypes.data_as(f64), rot.ctypes.data_as(f64), tp))
 
+    def halo_interp_sharded(self, plan):
+        """Second-order ghosts on a shard: ``plan`` = ``partition.InterpExchangePlan`` of this rank.  Replaces
+        ``halo_plan``; afterwards ``halo_push`` + ``halo_pull`` produce every ghost cell.  See ``cs_halo_interp_sharded``."""
+        i64, f64 = C.POINTER(C.c_int64), C.POINTER(C.c_double)
+        n = len(plan.send_counts)
+        sc = (C.c_int64 * n)(*plan.send_counts)
+        rc = (C.c_int64 * n)(*plan.recv_counts)
+        ss = np.ascontiguousarray(np.concatenate(plan.send_src) if n else np.empty(0), dtype=np.int64)
+        dst = np.ascontiguousarray(plan.dst, dtype=np.int64)
+        src = np.ascontiguousarray(plan.src, dtype=np.int64).reshape(-1, 4)
+        w = np.ascontiguousarray(plan.w, dtype=np.float64).reshape(-1, 4)
+        rot = np.ascontiguousarray(plan.rot, dtype=np.float64).reshape(-1, 4)
+        tang = np.ascontiguousarray(plan.tangents, dtype=np.float64)
+        self._check(self._lib.cs_halo_interp_sharded(self._h, n, sc, ss.ctypes.data_as(i64) if ss.size else None, rc, dst.shape[0],
+                                                     dst.ctypes.data_as(i64), src.ctypes.data_as(i64), w.ctypes.data_as(f64),
+                                                     rot.ctypes.data_as(f64), tang.ctypes.data_as(f64)))
+
     # -- step -----------------------------------------------------------------
     def set_topography(self, hs):
         if hs is None:
@@ -493,6 +510,18 @@ class Context:
             raise ValueError("need one handle block and one offset per rank")
         off = (C.c_int64 * n)(*[int(x) for x in remote_offsets])
         self._check(self._lib.cs_halo_peer_connect(self._h, n, int(my_rank), C.c_char_p(blob), off))
+
+    def halo_peer_pointers(self):
+        """(recv0, recv1, flags) device addresses of this context's exchange buffers: for contexts of one process."""
+        out = (C.c_void_p * 3)()
+        self._check(self._lib.cs_halo_peer_pointers(self._h, out))
+        return [int(x or 0) for x in out]
+
+    def halo_peer_connect_pointers(self, my_rank, all_pointers, remote_offsets):
+        n = len(all_pointers)
+        flat = (C.c_void_p * (3 * n))(*[p for trip in all_pointers for p in trip])
+        off = (C.c_int64 * n)(*[int(x) for x in remote_offsets])
+        self._check(self._lib.cs_halo_peer_connect_pointers(self._h, n, int(my_rank), flat, off))
 
     def halo_peer_timeouts(self):
         """Number of pulls that gave up waiting for a peer (0 in a healthy run)."""

@@ -190,3 +190,88 @@ def apply_code(u, v, code):
     a = np.where(swap, v, u)
     b = np.where(swap, u, v)
     return np.where(code & 2, -a, a), np.where(code & 4, -b, b)
+
+
+class InterpExchangePlan:
+    """Exchange plan of one rank for the SECOND-ORDER ghosts (geometry.seam_interp_tables) on a sharded sphere.
+
+    Every ghost cell is a weighted sum of four interior cells of a neighbouring face; on a shard those four may live on
+    this rank or on peers (and, with several tiles per face edge, on two different peers).  So the raw source cells
+    travel and the receiver interpolates: for every peer r, ``need[r]`` = the peer's cells this rank's ghost rows read
+    (sorted by global element offset, each once) and ``send_src[r]`` = this rank's cells peer r reads, in the order r
+    expects them.  Rows address their sources in one virtual space: offsets below ``field_elems`` are cells of the local
+    shard, ``field_elems + k`` is cell k of the receive buffer (peer blocks in rank order, 1 or 3 values per cell).
+    Everything is derived from the global table, so all ranks compute consistent plans without talking.
+
+    The NumPy methods emulate the device path (tests run all ranks in one process)."""
+
+    def __init__(self, N, p, g, rank, ranges, order=None, points=4):
+        from . import geometry
+        self.N, self.p, self.g, self.rank, self.ranges = N, p, g, rank, list(ranges)
+        n = N // p
+        m = n + 2 * g
+        te = m * m
+        n_all = topology.num_tiles(p)
+        order = np.arange(n_all) if order is None else np.asarray(order, dtype=np.int64)
+        pos_of = np.empty(n_all, dtype=np.int64)
+        pos_of[order] = np.arange(n_all)
+        world = len(self.ranges)
+        owner_of = np.empty(n_all, dtype=np.int64)
+        for r, (b, c) in enumerate(self.ranges):
+            owner_of[order[b:b + c]] = r
+        tab = geometry.seam_interp_tables(N, g, p, points)
+        self.tangents = tab["tangents"]
+        dst_tile = tab["dst"] // te
+        src_tile = tab["src"] // te                                  # [rows, 4]
+        dst_owner = owner_of[dst_tile]
+        src_owner = owner_of[src_tile]
+        t0 = [b for b, _ in self.ranges]
+
+        def local(glob, r):                                          # global element offset -> offset in rank r's shard
+            return (pos_of[glob // te] - t0[r]) * te + glob % te
+
+        # need[q][r]: global offsets of rank r's cells that rank q's rows read (sorted, unique)
+        need = [[None] * world for _ in range(world)]
+        for q in range(world):
+            rows = dst_owner == q
+            s, o = tab["src"][rows], src_owner[rows]
+            for r in range(world):
+                need[q][r] = np.unique(s[o == r]) if r != q else np.empty(0, dtype=np.int64)
+        self.recv_counts = [int(need[rank][r].size) for r in range(world)]
+        self.send_counts = [int(need[r][rank].size) for r in range(world)]
+        self.send_src = [local(need[r][rank], rank) for r in range(world)]
+        self.remote_offsets = [int(sum(need[r][q].size for q in range(rank))) for r in range(world)]
+        self.field_elems = self.ranges[rank][1] * te
+        mine = np.nonzero(dst_owner == rank)[0]
+        self.dst = local(tab["dst"][mine], rank)
+        src = tab["src"][mine]
+        own = src_owner[mine]
+        virt = np.empty_like(src)
+        loc = own == rank
+        virt[loc] = local(src[loc], rank)
+        roff = np.concatenate([[0], np.cumsum(self.recv_counts)])
+        for r in range(world):
+            sel = own == r
+            if r == rank or not sel.any():
+                continue
+            virt[sel] = self.field_elems + roff[r] + np.searchsorted(need[rank][r], src[sel])
+        self.src = virt
+        self.w, self.rot = tab["w"][mine], tab["rot"][mine]
+
+    # NumPy emulation: cells [cell, field] per peer
+    def pack(self, fields):
+        return [np.stack([f.reshape(-1)[idx] for f in fields], axis=-1) for idx in self.send_src]
+
+    def apply(self, blocks, fields):
+        """``blocks[r]``: what peer r packed for this rank, ``[recv_counts[r], nfields]``; fills every ghost cell."""
+        nf = len(fields)
+        recv = np.concatenate([np.asarray(b).reshape(-1, nf) for b in blocks]) if sum(self.recv_counts) else np.zeros((0, nf))
+        out = []
+        for k, f in enumerate(fields):
+            flat = f.reshape(-1)
+            virt = np.concatenate([flat, recv[:, k]])
+            out.append(np.sum(self.w * virt[self.src], -1))
+        fields[0].reshape(-1)[self.dst] = out[0]
+        if nf == 3:
+            fields[1].reshape(-1)[self.dst] = self.rot[:, 0, 0] * out[1] + self.rot[:, 0, 1] * out[2]
+            fields[2].reshape(-1)[self.dst] = self.rot[:, 1, 0] * out[1] + self.rot[:, 1, 1] * out[2]

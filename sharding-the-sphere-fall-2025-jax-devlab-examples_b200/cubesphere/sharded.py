@@ -37,7 +37,12 @@ RK_PAIRS = {
 class ShardedStepper:
     def __init__(self, N, tiles_per_edge=1, halo=2, dtype="f32", rk="ssprk3", limiter="mc", advect_only=False,
                  axis=(0.0, 0.0, 1.0), device=0, rank=0, world=1, kernel="auto", tangents=None, overlap=True,
-                 group=None, use_graph=True, sums_of_entry_state=False, halo_path="peer", tile_map="locality"):
+                 group=None, use_graph=True, sums_of_entry_state=False, halo_path="peer", tile_map="locality",
+                 second_order=False):
+        # second_order: ghost values interpolated to this panel's own extended grid instead of copied --
+        # second order at the seams, mass no longer to round-off.  On several GPUs it needs the one-sided exchange
+        # (raw cells travel, the receiver interpolates).
+        self.second_order = bool(second_order)
         # sums_of_entry_state: step(..., diag) reports mass / energy of the state the step STARTS from, summed inside
         # the first stage's launches (a few instructions per cell); default: of the new state, inside the last stage's
         self.sums_of_entry_state = bool(sums_of_entry_state)
@@ -73,9 +78,20 @@ class ShardedStepper:
         self._extra_launches = 0
         self._sums_where = os.environ.get("CS_SUMS_WHERE", "own_stream")       # tuning knob: own_stream | comm_stream
         self._skip_exchange = False      # measurement only (time_halo): a step with the cross-GPU exchange left out
+        if world == 1 and self.second_order:
+            from . import geometry
+            self.ctx.set_halo_interpolation(geometry.seam_interp_tables(N, halo, tiles_per_edge))
         if world > 1:
-            self.send_counts, self.recv_counts = self.ctx.halo_plan([b for b, _ in self.ranges],
-                                                                    [c for _, c in self.ranges])
+            if self.second_order:
+                if halo_path != "peer":
+                    raise ValueError("second_order on several GPUs needs halo_path='peer'")
+                from .partition import InterpExchangePlan
+                plan = InterpExchangePlan(N, tiles_per_edge, halo, rank, self.ranges, self.ctx.tile_order)
+                self.ctx.halo_interp_sharded(plan)
+                self.send_counts, self.recv_counts = plan.send_counts, plan.recv_counts
+            else:
+                self.send_counts, self.recv_counts = self.ctx.halo_plan([b for b, _ in self.ranges],
+                                                                        [c for _, c in self.ranges])
             dev = f"cuda:{device}"
             self.sendbuf = torch.zeros(max(1, 3 * sum(self.send_counts)), dtype=self.ctx.dtype, device=dev)
             self.recvbuf = torch.zeros(max(1, 3 * sum(self.recv_counts)), dtype=self.ctx.dtype, device=dev)
@@ -102,6 +118,8 @@ class ShardedStepper:
             self._peer = False
             if halo_path == "peer":
                 self._peer = self._connect_peers()
+                if self.second_order and not self._peer:
+                    raise RuntimeError("second_order needs the one-sided exchange, and the peers' buffers could not be mapped")
             self.halo_path = ("peer stores into the neighbours' receive buffers (CUDA IPC over NVLink) + flag, then pull"
                               if self._peer else "pack -> NCCL all_to_all_single -> unpack")
             if self._peer and "CS_MARCH_RESERVE_SMS" not in os.environ:

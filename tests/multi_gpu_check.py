@@ -20,7 +20,7 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ok = True
 for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "peer"), (96, 2, True, True, "peer"), (96, 2, True, True, "peer-block"),
                                    (96, 2, True, False, "nccl"), (96, 2, "side", True, "peer"), (96, 2, "side", False, "nccl"),
-                                   (96, 2, False, False, "peer"), (96, 2, False, True, "nccl")):
+                                   (96, 2, False, False, "peer"), (96, 2, False, True, "nccl"), (96, 2, True, True, "peer-2nd")):
     if (6 * p * p) % world:
         continue
     g, steps = 2, 10
@@ -29,7 +29,16 @@ for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "pee
     ref = orc.halo_fill_state(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g), g)
     st = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype="f64", axis=case.axis, device=local, rank=rank,
                                 world=world, tangents=orc.centre_tangents(N), overlap=overlap, sums_of_entry_state=entry, halo_path=path.split("-")[0],
-                                tile_map="block" if path.endswith("-block") else "locality")
+                                tile_map="block" if path.endswith("-block") else "locality", second_order=path.endswith("-2nd"))
+    if path.endswith("-2nd"):
+        # second-order ghosts: the oracle is the study's statement of the same construction on whole faces
+        from oracle import seam_study
+        halo2 = seam_study.SeamHalo(N, g, "interp")
+        par = orc.Params(N, g, axis=case.axis, hs=None, tangents=halo2.tangents, halo_fill=halo2)
+        hs2 = orc.pad(case.hs, g)
+        halo2(hs2, np.zeros_like(hs2), np.zeros_like(hs2))
+        par.hs = hs2
+        ref = halo2(orc.pad(case.h, g), orc.pad(case.u1, g), orc.pad(case.u2, g))
     if path.startswith("peer") and "peer stores" not in st.halo_path:
         print(f"rank {rank}: the peer path fell back to NCCL ({st.halo_path})", flush=True)
         ok = False
@@ -57,7 +66,9 @@ for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "pee
         errs.append(float(np.linalg.norm(a[:, g:g + n, :] - w[:, g:g + n, :]) / np.linalg.norm(w[:, g:g + n, :])))
     mo = orc.diagnostics(par, *ref)
     mfo = mo_entry if entry else mo                    # entry mode: the fused sums are those of the state before the last step
-    good = max(errs) <= 1e-12 and abs(m1[0] - m0[0]) <= 1e-13 * m0[0] and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
+    # (the second-order ghosts do not keep mass to round-off: there the drift is only held to the oracle's)
+    drift_ok = path.endswith("-2nd") or abs(m1[0] - m0[0]) <= 1e-13 * m0[0]
+    good = max(errs) <= 1e-12 and drift_ok and abs(m1[0] - mo[0]) <= 1e-13 * mo[0]
     good = good and abs(mf[0] - mfo[0]) <= 1e-13 * mfo[0] and abs(mf[1] - mfo[1]) <= 1e-12 * abs(mfo[1])
     # deferred sums: three more steps recorded on the device, one all-reduce when read
     rec_ref = []

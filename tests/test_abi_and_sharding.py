@@ -248,3 +248,53 @@ def test_c_caller_runs_on_the_gpu(built_library, tmp_path):
     r = subprocess.run([str(exe), "48", "10"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, (r.stdout, r.stderr)
     assert "max |h - h0| = 0.000e+00" in r.stdout and "max |u| = 0.000e+00" in r.stdout, r.stdout
+
+
+@pytest.mark.parametrize("tile_map", ["block", "locality"])
+@pytest.mark.parametrize("N,p,world", [(12, 1, 2), (12, 2, 4), (16, 2, 8), (12, 1, 6)])
+def test_interp_exchange_plan_serial_emulation(N, p, world, tile_map):
+    """Second-order ghosts on a sharded sphere: every rank packs the raw cells its peers' rows read, receives its own and
+    interpolates -- the edge ghosts equal those of the oracle study's whole-sphere construction to round-off, and every
+    ghost cell equals the product's whole-sphere tables applied on one device."""
+    from cubesphere import geometry as geo
+    from oracle import seam_study
+    g = 2
+    order = np.arange(6 * p * p) if tile_map == "block" else partition.locality_order(p, world)
+    rng = np.random.default_rng(9)
+    M = N + 2 * g
+    faces = [rng.standard_normal((6, M, M)) for _ in range(3)]
+    tiles = [orc.faces_to_tiles(x, p, g) for x in faces]
+    n = N // p
+    m = n + 2 * g
+    # reference 1: the whole-sphere product tables in NumPy
+    tab = geo.seam_interp_tables(N, g, p)
+    want = [x.copy() for x in tiles]
+    flat = [x.reshape(-1) for x in tiles]
+    gh, ga, gb = (np.sum(tab["w"] * f[tab["src"]], -1) for f in flat)
+    want[0].reshape(-1)[tab["dst"]] = gh
+    want[1].reshape(-1)[tab["dst"]] = tab["rot"][:, 0, 0] * ga + tab["rot"][:, 0, 1] * gb
+    want[2].reshape(-1)[tab["dst"]] = tab["rot"][:, 1, 0] * ga + tab["rot"][:, 1, 1] * gb
+    ranges = partition.block_ranges(6 * p * p, world)
+    plans = [partition.InterpExchangePlan(N, p, g, r, ranges, order) for r in range(world)]
+    shards = [[np.ascontiguousarray(x[order[b:b + c]]) for x in tiles] for b, c in ranges]
+    for r in range(world):
+        for q in range(world):
+            assert plans[r].send_counts[q] == plans[q].recv_counts[r]
+            assert plans[r].remote_offsets[q] == sum(plans[q].recv_counts[:r])
+    packed = [pl.pack(sh) for pl, sh in zip(plans, shards)]
+    for r, (pl, sh) in enumerate(zip(plans, shards)):
+        pl.apply([packed[q][r] for q in range(world)], sh)
+        b, c = ranges[r]
+        for got, w in zip(sh, want):
+            assert np.abs(got - w[order[b:b + c]]).max() <= 1e-13
+    # reference 2 (p = 1 only: the study works on whole faces): the oracle's independent construction, edge strips
+    if p == 1:
+        halo = seam_study.SeamHalo(N, g, "interp")
+        ref = halo(*(x.copy() for x in faces))
+        for r, sh in enumerate(shards):
+            b, c = ranges[r]
+            for got, w in zip(sh, ref):
+                wt = orc.faces_to_tiles(w, p, g)[order[b:b + c]].reshape(-1)
+                d = np.isin(np.arange(wt.size), plans[r].dst) & np.isin((np.arange(wt.size) + b * m * m) if tile_map == "block" else np.full(wt.size, -1), halo.dst)
+                if tile_map == "block":
+                    assert np.abs(got.reshape(-1)[d] - wt[d]).max() <= 1e-13

@@ -573,3 +573,102 @@ def test_step_sums_for_every_scheme(built_library, rk, entry):
     c = slice(g, g + N)
     assert np.linalg.norm(dev[0].cpu().numpy()[:, c, c] - ref[0][:, c, c]) <= 1e-13 * np.linalg.norm(ref[0][:, c, c])
     ctx.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the one-sided exchange with every rank's context in this process (pointers instead of IPC handles)
+# ---------------------------------------------------------------------------------------------------------------
+
+def _connect_in_process(ctxs, recv_counts):
+    """recv_counts[r][q] = cells rank r receives from rank q."""
+    for c in ctxs:
+        c.halo_peer_alloc()
+    ptrs = [c.halo_peer_pointers() for c in ctxs]
+    world = len(ctxs)
+    for r, c in enumerate(ctxs):
+        c.halo_peer_connect_pointers(r, ptrs, [sum(recv_counts[q][:r]) for q in range(world)])
+
+
+@pytest.mark.parametrize("second_order", [False, True])
+@pytest.mark.parametrize("p,world,tile_map", [(1, 2, "block"), (2, 4, "locality"), (2, 8, "locality"), (2, 8, "block")])
+def test_one_sided_exchange_emulated_on_one_gpu(built_library, p, world, tile_map, second_order):
+    """halo_push / halo_pull (the kernels of the multi-GPU exchange) with all ranks on this GPU: pushes store into the other
+    contexts' receive buffers and raise their flags, pulls wait for the flags and fill the ghosts.  Copy ghosts: bit-exact
+    against the oracle's fill.  Second-order ghosts: raw cells travel, the receiver interpolates -- bit-identical to the
+    whole-sphere context with the same tables.  Two fills in a row (both buffer parities), then three steps."""
+    from cubesphere import geometry as geo, partition
+    from cubesphere.sharded import RK_PAIRS
+    N, g = 48, 2
+    n, m = N // p, N // p + 2 * g
+    case = cases.make_case("tc2", N, alpha0=0.6)
+    order = np.arange(6 * p * p) if tile_map == "block" else partition.locality_order(p, world)
+    ranges = partition.block_ranges(6 * p * p, world)
+    tang = orc.centre_tangents(N)
+    whole = api.Context(N, tiles_per_edge=p, halo=g, axis=case.axis, tangents=tang)
+    if second_order:
+        whole.set_halo_interpolation(geo.seam_interp_tables(N, g, p))
+    ctxs, recv_counts = [], []
+    for r, (b, c) in enumerate(ranges):
+        ctx = api.Context(N, tiles_per_edge=p, halo=g, axis=case.axis, tangents=tang, tile_begin=b, tile_count=c, tile_order=order)
+        if second_order:
+            plan = partition.InterpExchangePlan(N, p, g, r, ranges, order)
+            ctx.halo_interp_sharded(plan)
+            recv_counts.append(plan.recv_counts)
+        else:
+            _, recv = ctx.halo_plan([x for x, _ in ranges], [x for _, x in ranges])
+            recv_counts.append(recv)
+        ctxs.append(ctx)
+    _connect_in_process(ctxs, recv_counts)
+    rng = np.random.default_rng(2)
+    for trial in range(2):
+        tiles = [np.ascontiguousarray(rng.standard_normal((6 * p * p, m, m))) for _ in range(3)]
+        ref = [torch.from_numpy(x.copy()).cuda() for x in tiles]
+        whole.halo_fill_state(*ref)
+        shards = []
+        for r, (b, c) in enumerate(ranges):
+            sh = []
+            for x in tiles:
+                y = np.full((c, m, m), np.nan)
+                y[:, g:g + n, g:g + n] = x[order[b:b + c]][:, g:g + n, g:g + n]
+                sh.append(torch.from_numpy(y).cuda())
+            shards.append(sh)
+        for ctx, sh in zip(ctxs, shards):
+            ctx.halo_fill_state(*sh)
+        for ctx, sh in zip(ctxs, shards):
+            ctx.halo_push(*sh)
+        for ctx, sh in zip(ctxs, shards):
+            ctx.halo_pull(*sh)
+        idx = torch.from_numpy(order.astype(np.int64)).cuda()
+        for (b, c), sh in zip(ranges, shards):
+            for got, want in zip(sh, ref):
+                assert torch.equal(got, want[idx[b:b + c]])
+    assert all(c.halo_peer_timeouts() == 0 for c in ctxs)
+    # three steps of the steady case, stage by stage as the sharded stepper runs them
+    par_ref = [torch.from_numpy(orc.faces_to_tiles(orc.pad(x, g), p, g)).cuda() for x in (case.h, case.u1, case.u2)]
+    whole.halo_fill_state(*par_ref)
+    state = [[x[idx[b:b + c]].contiguous() for x in par_ref] for b, c in ranges]
+    qa = [[c.new_field() for _ in range(3)] for c in ctxs]
+    qb = [[c.new_field() for _ in range(3)] for c in ctxs]
+    dt = cases.stable_dt(case, 0.5)
+    for _ in range(3):
+        whole.step(*par_ref, dt)
+        cur = state
+        for k, (a, bb) in enumerate(RK_PAIRS["ssprk3"]):
+            out = state if k == 2 else (qa if k == 0 else qb)
+            for r, ctx in enumerate(ctxs):
+                ctx.rk_stage(state[r], cur[r], out[r], a, bb, dt, part=1)
+                ctx.rk_stage(state[r], cur[r], out[r], a, bb, dt, part=0)
+                ctx.halo_fill_state(*out[r])
+            for r, ctx in enumerate(ctxs):
+                ctx.halo_push(*out[r])
+            for r, ctx in enumerate(ctxs):
+                ctx.halo_pull(*out[r])
+            cur = out
+    for (b, c), sh in zip(ranges, state):
+        for got, want in zip(sh, par_ref):
+            w = want[idx[b:b + c]]
+            assert float((got - w)[:, g:g + n, g:g + n].abs().max()) <= 1e-13 * float(w.abs().max())
+    torch.cuda.synchronize()
+    for c in ctxs:
+        c.close()
+    whole.close()
