@@ -55,6 +55,8 @@ def parse_args():
                     help="per-step mass / energy of the NEW state (summed in the last stage) instead of the entry state (first stage)")
     ap.add_argument("--overlap", default="side", choices=["side", "rim_first", "none"],
                     help="N > 1: how a stage is split (rim kernel first on the whole GPU, or on a side stream beside the inner kernel)")
+    ap.add_argument("--second-order", action="store_true",
+                    help="interpolated (second-order) ghosts instead of the conservative copy (DESIGN.md 3.5); not the headline configuration")
     ap.add_argument("--tile-map", default="locality", choices=["locality", "block"],
                     help="N > 1: order of the tiles along the sharded axis (compact blocks, or the reference's plain order)")
     ap.add_argument("--halo-path", default="peer", choices=["peer", "nccl"],
@@ -350,7 +352,8 @@ def run_ours(args):
     stepper = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
                                      advect_only=case.advect_only, device=local, rank=rank, world=world,
                                      kernel=args.kernel, sums_of_entry_state=not args.new_state_sums, halo_path=args.halo_path,
-                                     overlap=False if args.overlap == "none" else args.overlap, tile_map=args.tile_map)
+                                     overlap=False if args.overlap == "none" else args.overlap, tile_map=args.tile_map,
+                                     second_order=args.second_order)
     assert (stepper.tile_begin, stepper.tile_count) == (t0, tc)
 
     def padded(field):
@@ -478,7 +481,7 @@ def run_ours(args):
                 "what": "exchange_us = the cross-GPU part of one ghost fill (push + pull, or pack + all-to-all + unpack), alone on an idle GPU, max over ranks; "
                         "exposed = step time minus the time of the same step with the cross-GPU exchange left out",
                 "path": stepper.halo_path}
-        if "peer stores" in stepper.halo_path and not args.no_secondary:
+        if "peer stores" in stepper.halo_path and not args.no_secondary and not args.second_order:
             # the comparison arm: the same job with pack -> NCCL all-to-all -> unpack
             alt = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
                                          advect_only=case.advect_only, device=local, rank=rank, world=world,
@@ -603,6 +606,7 @@ def run_ours(args):
                                         "per timed region (inside the timing) combines the record across GPUs"),
                        "l2": "state (3 x %.0f MB x 3 buffers per GPU) is larger than L2; no flush needed" %
                              (cells_local * esize / 1e6),
+                       "ghosts": "second order: interpolated + rotated, extended metric" if args.second_order else "copy + signed permutation (bit-exact, conservative)",
                        "finite": finite},
             "ms_per_step_without_sums": ms_nosums / args.steps, "diag": d_after,
             "roofline": roofline, "halo": halo, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
