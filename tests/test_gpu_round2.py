@@ -545,8 +545,11 @@ def test_cli_diffusion_demo_and_second_order_flag(built_library, capsys):
     assert abs(totals[-1] - totals[-3]) <= 1e-12 * totals[-1]          # no source in the second half: heat conserved
     run.main(["--case", "tc2", "--N", "24", "--hours", "2", "--second-order", "--limiter", "none"])
     out = capsys.readouterr().out
-    drift = float(out.strip().splitlines()[-2].split("mass drift =")[1].split()[0])
+    lines = out.strip().splitlines()
+    drift = float([l for l in lines if "mass drift =" in l][-1].split("mass drift =")[1].split()[0])
     assert 0 < abs(drift) < 1e-5                                        # truncation-level, not round-off, and small
+    err = float([l for l in lines if "steady case" in l][-1].split("=")[1])
+    assert 0 < err < 1e-3                                               # two hours of a steady flow at C24
 
 
 @pytest.mark.parametrize("rk", ["euler", "ssprk2", "ssprk3"])
