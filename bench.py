@@ -424,6 +424,14 @@ def run_ours(args):
     roof = stepper.time_stage_kernel(dev, dt, reps=10)
     words = {True: 6, False: 9}                    # stage 1 reads qs, writes out; later stages also read q0
     alg_bytes = sum(words[a == 0.0] for a in roof["a"]) * esize * cells_local
+    # the launches of the TIMED step: the stage that also forms the conservation sums is timed with them (at N > 1 the
+    # stages are split into inner + rim launches and the whole-cell launch is timed without sums)
+    stage_ms_nosums = [float(x) for x in roof["ms"]]
+    if roof["fused_sums_us"] is not None:
+        if args.new_state_sums:
+            roof["ms"][-1] += roof["fused_sums_us"]["of_new_state_in_last_stage"] * 1e-3
+        else:
+            roof["ms"][0] += roof["fused_sums_us"]["of_entry_state_in_first_stage"] * 1e-3
     achieved = alg_bytes / (sum(roof["ms"]) * 1e-3) / 1e9
     # traffic: dram__bytes_read + dram__bytes_write per launch from the committed `ncu --set full` capture of
     # this kernel (profiles/r0N_traffic.json); only quoted when the capture's configuration is the one running
@@ -444,6 +452,8 @@ def run_ours(args):
                 "algorithmic_bytes_per_cell_step": 24 * esize,
                 "stage_ms": [float(x) for x in roof["ms"]],
                 "stage_frac": [words[a == 0.0] * esize * cells_local / (t * 1e-3) / 1e9 / peak for a, t in zip(roof["a"], roof["ms"])],
+                "stage_ms_without_sums": stage_ms_nosums,
+                "frac_without_sums": alg_bytes / (sum(stage_ms_nosums) * 1e-3) / 1e9 / peak,
                 "fused_sums_us": roof["fused_sums_us"],
                 "frac_of_nominal_8TBs": achieved / 8000.0,
                 "whole_step_frac": step_bytes / (ms / args.steps * 1e-3) / 1e9 / peak,
@@ -570,6 +580,9 @@ def run_ours(args):
         torch.cuda.synchronize()
         ms64 = ev0.elapsed_time(ev1)
         r64 = st64.time_stage_kernel(d64, dt, reps=10)
+        if r64["fused_sums_us"] is not None:        # as above: the stage that forms the sums is timed with them
+            k64, key64 = (-1, "of_new_state_in_last_stage") if args.new_state_sums else (0, "of_entry_state_in_first_stage")
+            r64["ms"][k64] += r64["fused_sums_us"][key64] * 1e-3
         ach64 = sum(words[a == 0.0] for a in r64["a"]) * 8 * cells_local / (sum(r64["ms"]) * 1e-3) / 1e9
         secondary = {"dtype": "f64", "value": cells_total * args.steps / (ms64 * 1e-3), "unit": UNIT,
                      "ms_per_step": ms64 / args.steps, "roofline_frac": ach64 / peak, "achieved_GBps": ach64,

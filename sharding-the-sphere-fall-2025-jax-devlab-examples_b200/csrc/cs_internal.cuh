@@ -40,7 +40,7 @@ struct CsTuning {
     int march_prefetch = 2;      // CS_MARCH_PREFETCH: L2 prefetch distance in rows
     int march_rows = 0;          // CS_MARCH_ROWS: strip height, 0 = wave-aware heuristic
     int march_vec = 4;           // CS_MARCH_VEC: fp32 columns per thread (4 | 2)
-    int march_unit = 1;          // CS_MARCH_UNIT: fp64 first-stage variant
+    int march_unit = 1;          // CS_MARCH_UNIT: first-stage build (0 never, 1 fp64 + fp32 launches without sums, 2 always)
     int reserve_sms = 12;        // CS_MARCH_RESERVE_SMS: SMs left to the exchange stream by a split stage
     int tma_ring = 6;            // CS_TMA_RING
     int fused_halo = 1;          // CS_FUSED_HALO: 0 vetoes cfg.fused_halo

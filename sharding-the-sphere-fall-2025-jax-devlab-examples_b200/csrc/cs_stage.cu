@@ -14,6 +14,15 @@
 
 using namespace cs_launch;
 
+// resident blocks per SM the fp32 four-column build is compiled for (tuning aid: 3 caps the kernel at 168 registers)
+#ifndef CS_MINB_F32V4
+#define CS_MINB_F32V4 2
+#endif
+// ... and the same for its first-stage (UNIT) build, which needs fewer registers (no q0 in flight)
+#ifndef CS_MINB_UNIT_F32V4
+#define CS_MINB_UNIT_F32V4 CS_MINB_F32V4
+#endif
+
 namespace {
 
 // ---------------------------------------------------------------------------------------------
@@ -114,10 +123,32 @@ int launch_march(cs_ctx* ctx, const StageParams<R>& P, int lo, int hi, double* d
     const StageParams<R>& PP = P;
     const int warps = CS_MARCH_THREADS / 32;
     // First stage, (a, b) = (0, 1): a variant compiled without q0 and without the multiplications by b.  11 % fewer
-    // instructions in both precisions, but only fp64 gains (169 -> 154 us at C1536); the fp32 build of it is
-    // 7 % SLOWER than the general kernel (87 vs 81 us: a different schedule, not fewer stalls), so fp32 does not use it.
-    // march_unit: 0 never, 1 fp64 only (default), 2 fp32 as well (re-measured after each change of the kernel)
-    const bool unit_variant = sizeof(R) == 8 ? ctx->tune.march_unit >= 1 : ctx->tune.march_unit >= 2;
+    // instructions in both precisions.  fp64 gains either way (169 -> 154 us at C1536).  fp32 gains without the sums
+    // (74.7 vs 80.9 us) and loses with the entry-state sums in the same launch (whole step 0.289 vs 0.286 ms): a
+    // different schedule, not fewer stalls -- re-measured after each change of the kernel (tools/ab_stage.py, ab_step.py).
+    // march_unit: 0 never; 1 (default) fp64 always, fp32 for the launches without sums; 2 always
+    const bool with_sums = diag_out != nullptr && sums_in != 0;
+    const bool unit_variant = sizeof(R) == 8 ? ctx->tune.march_unit >= 1
+                                             : (ctx->tune.march_unit >= 2 || (ctx->tune.march_unit == 1 && !with_sums));
+    constexpr int MU = (sizeof(R) == 4 && V == 4) ? CS_MINB_UNIT_F32V4 : MINB;
+    if (MU != MINB && unit_variant && P.a == R(0) && P.b == R(1) && !P.push) {
+        // the first-stage build is compiled for another occupancy: its own work decomposition
+        const MarchGeom GU = march_geometry(ctx, stage_march_kernel<R, V, LIM, MU, false, true>, V, P.n, P.g, P.m, P.T, lo, hi, 0);
+        const dim3 gridu((GU.nitems + warps - 1) / warps), blocku(CS_MARCH_THREADS);
+        if (diag_out && sums_in && ctx->tune.fused_diag && GU.nitems <= ctx->partial_cap) {
+            StageParams<R> Q = PP;
+            Q.partials = ctx->d_partials, Q.ticket = ctx->d_ticket, Q.diag_out = diag_out, Q.sums_in = sums_in;
+            CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MU, false, true, 2>, gridu, blocku, 0, s, ctx->pdl, Q, GU));
+            ctx->stage_diag_fused = true;
+            ctx->launches++;
+            return CS_OK;
+        }
+        if (!diag_out) {
+            CS_CUDA(ctx, cs_launch_dependent(stage_march_kernel<R, V, LIM, MU, false, true>, gridu, blocku, 0, s, ctx->pdl, PP, GU));
+            ctx->launches++;
+            return CS_OK;
+        }
+    }
     const dim3 grid((G.nitems + warps - 1) / warps), block(CS_MARCH_THREADS);
     if (diag_out && !P.push && ctx->tune.fused_diag && G.nitems <= ctx->partial_cap) {
         // last stage of a step: the conservation sums of the output come out of the same launch (K3 fused into K2)
@@ -214,7 +245,7 @@ int launch_lim(cs_ctx* ctx, const StageParams<R>& P0, int part, double* diag_out
     // fp32: four columns per thread (one 16-byte access per row and variable) when rows allow it, else two;
     // fp64: two.  CS_MARCH_VEC=2 forces the two-column fp32 variant (tuning aid).
     if constexpr (sizeof(R) == 4) {
-        if (ctx->tune.march_vec == 4 && P.m % 4 == 0) return launch_march<R, 4, LIM, 2>(ctx, Q, lo, hi, diag_out, sums_in, s);
+        if (ctx->tune.march_vec == 4 && P.m % 4 == 0) return launch_march<R, 4, LIM, CS_MINB_F32V4>(ctx, Q, lo, hi, diag_out, sums_in, s);
         return launch_march<R, 2, LIM, 4>(ctx, Q, lo, hi, diag_out, sums_in, s);
     } else {
         return launch_march<R, 2, LIM, 2>(ctx, Q, lo, hi, diag_out, sums_in, s);
