@@ -2,6 +2,8 @@
 
     python -m cubesphere.run --case tc5 --N 384 --hours 24 --dtype f64 [--restart out.npz]
     python -m cubesphere.run --resume out.npz --hours 24 [--restart out2.npz]      # carry on from a restart file
+    python -m cubesphere.run --case tc6 --N 192 --hours 48 --history run.zarr --history-every 100   # zarr v2 history
+    python -m cubesphere.run --resume run.zarr --hours 24                          # ... and carry on from its last record
     python -m cubesphere.run --case tc2 --N 96 --second-order                      # interpolated ghosts
     python -m cubesphere.run --demo diffusion --N 96 --steps 2000                  # the reference's heat-diffusion demo
 
@@ -26,7 +28,10 @@ def main(argv=None):
     ap.add_argument("--limiter", default="mc", choices=["none", "minmod", "mc"])
     ap.add_argument("--report-every", type=int, default=50)
     ap.add_argument("--restart", default=None, help="write the final state to this .npz file")
-    ap.add_argument("--resume", default=None, help="start from this restart file (case, N, dtype are taken from it)")
+    ap.add_argument("--resume", default=None,
+                    help="start from this restart file, or from the last record of a history directory (case, N, dtype are taken from it)")
+    ap.add_argument("--history", default=None, help="append records to this zarr v2 directory store (cubesphere.history)")
+    ap.add_argument("--history-every", type=int, default=100, help="steps between history records")
     ap.add_argument("--second-order", action="store_true",
                     help="ghost values interpolated to our own extended grid (second order at the seams; mass drifts at truncation level)")
     ap.add_argument("--demo", default=None, choices=["diffusion"],
@@ -35,7 +40,8 @@ def main(argv=None):
     args = ap.parse_args(argv)
 
     import torch
-    from . import api, cases, geometry, io
+    from pathlib import Path
+    from . import api, cases, geometry, history, io
 
     if args.demo == "diffusion":
         return diffusion_demo(args)
@@ -43,7 +49,10 @@ def main(argv=None):
     g = 2
     resumed, step0, time0 = None, 0, 0.0
     if args.resume:
-        resumed, meta = io.load_state(args.resume)
+        if Path(args.resume).is_dir():
+            resumed, meta = history.ZarrHistory.open(args.resume).read(-1)
+        else:
+            resumed, meta = io.load_state(args.resume)
         if meta["tiles_per_edge"] != 1 or meta["halo"] != g or not meta.get("case"):
             raise ValueError(f"{args.resume}: need a whole-face state with halo {g} and a named case")
         args.case, args.N = meta["case"], meta["N"]
@@ -73,10 +82,22 @@ def main(argv=None):
     h_start = h.clone() if args.case == "tc2" else None      # case 2 is steady: the initial state is the exact solution
     print(f"{args.case} C{args.N} {args.dtype}: dt = {dt:.2f} s, {nsteps} steps from step {step0}, "
           f"mass0 = {d0[0]:.6e}, energy0 = {d0[1]:.6e}")
+    hist = None
+    if args.history:
+        hp = Path(args.history)
+        hist = (history.ZarrHistory.open(hp) if (hp / ".zgroup").exists() else
+                history.ZarrHistory.create(hp, N=args.N, halo=g, dtype=ndt, case=args.case))
+        if (hist.N, hist.p, hist.g, hist.dtype) != (args.N, 1, g, np.dtype(ndt)):
+            raise ValueError(f"{hp}: the store holds another grid or precision")
+        if len(hist) == 0 or hist.read(-1)[1]["step"] < step0:
+            hist.append({"h": h, "u": u, "v": v}, step=step0, time=time0, mass=d0[0], energy=d0[1])
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for k in range(1, nsteps + 1):
         ctx.step(h, u, v, dt)
+        if hist is not None and (k % args.history_every == 0 or k == nsteps):
+            d = ctx.diagnostics(h, u, v).cpu().numpy()
+            hist.append({"h": h, "u": u, "v": v}, step=step0 + k, time=time0 + k * dt, mass=d[0], energy=d[1])
         if k % args.report_every == 0 or k == nsteps:
             d = ctx.diagnostics(h, u, v).cpu().numpy()
             print(f"  step {step0 + k:6d}  t = {(time0 + k * dt) / 3600.0:8.2f} h  mass drift = {(d[0] - d0[0]) / d0[0]:+.2e}  "
@@ -88,6 +109,8 @@ def main(argv=None):
         c = slice(g, g + args.N)
         err = float(torch.linalg.norm((h - h_start)[:, c, c].double()) / torch.linalg.norm(h_start[:, c, c].double()))
         print(f"steady case: relative L2 error of h against the exact solution = {err:.3e}")
+    if hist is not None:
+        print(f"{len(hist)} records in {args.history}")
     if args.restart:
         io.save_state(args.restart, {"h": h, "u": u, "v": v}, N=args.N, halo=g, step=step0 + nsteps,
                       time=time0 + nsteps * dt, case=args.case)

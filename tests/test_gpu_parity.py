@@ -523,3 +523,23 @@ def test_cli_resume_continues_bit_for_bit(built_library, tmp_path, capsys):
     for k in ("h", "u", "v"):
         assert np.array_equal(sb[k], sc[k])
     assert "from step" in capsys.readouterr().out
+
+
+def test_cli_history_store_and_resume_from_it(built_library, tmp_path, capsys):
+    """--history writes a zarr v2 store (first state, every k-th step, last step); --resume <store> carries on from its
+    last record, bit for bit, and appends to the same store."""
+    from cubesphere import history, io, run
+    store, c = str(tmp_path / "run.zarr"), str(tmp_path / "c.npz")
+    run.main(["--case", "tc5", "--N", "24", "--hours", "1", "--history", store, "--history-every", "4"])
+    hist = history.ZarrHistory.open(store)
+    assert hist.scalars()["step"].tolist() == [0, 4, 6]
+    run.main(["--resume", store, "--hours", "1", "--history", store, "--history-every", "4"])
+    run.main(["--case", "tc5", "--N", "24", "--hours", "2", "--restart", c])
+    sc_, mc = io.load_state(c)
+    sb, mb = hist.read(-1)
+    assert hist.scalars()["step"].tolist() == [0, 4, 6, 10, 12] and mb["step"] == mc["step"] == 12
+    for k in ("h", "u", "v"):
+        assert np.array_equal(sb[k], sc_[k])
+    m = hist.scalars()["mass"]
+    assert np.all(np.abs(m - m[0]) <= 1e-13 * m[0])           # the record carries the conservation sums
+    capsys.readouterr()
