@@ -358,6 +358,26 @@ class ShardedStepper:
             dist.all_reduce(out, group=self.group)
         return out
 
+    def write_history(self, hist, h, u, v, *, step, time):
+        """Append the current state to a :class:`cubesphere.history.ZarrHistory` (every rank opens the same store on a
+        shared file system).  Each rank writes the chunk files of the tiles it owns straight from its shard -- the
+        fields are never gathered; rank 0 adds the scalars (with the whole-sphere mass / energy) and publishes the record
+        after a barrier.  Synchronises; not for the timed path."""
+        sums = self.diagnostics(h, u, v).cpu().numpy()
+        record = len(hist)                                      # the same on every rank: nothing is published yet
+        if self.world > 1:
+            dist.barrier(group=self.group)                      # ... and nobody publishes before everybody has read it
+        ids = self.tiles
+        if self.rank != 0:
+            hist.append({"h": h, "u": u, "v": v}, step=step, time=time, tile_ids=ids, write_meta=False, record=record)
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        if self.rank == 0:
+            hist.append({"h": h, "u": u, "v": v}, step=step, time=time, mass=sums[0], energy=sums[1], tile_ids=ids, record=record)
+        if self.world > 1:
+            dist.barrier(group=self.group)
+        return record
+
     # -- measurement helpers used by bench.py ---------------------------------------------------
     def time_stage_kernel(self, state, dt, reps=10, rounds=3):
         """Device time of each fused-stage launch alone (all owned cells, no halo): ``reps`` launches of one stage

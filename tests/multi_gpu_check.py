@@ -81,6 +81,28 @@ for N, p, overlap, entry, path in ((48, 2 if world > 3 else 1, True, False, "pee
     rec = st.read_sums().cpu().numpy()
     good = good and rec.shape == (3, 2) and all(abs(rec[k, 0] - rec_ref[k][0]) <= 1e-13 * rec_ref[k][0] and
                                                 abs(rec[k, 1] - rec_ref[k][1]) <= 1e-12 * abs(rec_ref[k][1]) for k in range(3))
+    if path == "peer-block" or path == "peer" and overlap == "side":
+        # history: every rank writes the chunks of its own tiles, rank 0 publishes; read back whole and compared
+        import tempfile
+        from cubesphere import history
+        box = [tempfile.mkdtemp(prefix="cs_hist_") if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        store = Path(box[0]) / "run.zarr"
+        if rank == 0:
+            history.ZarrHistory.create(store, N=N, tiles_per_edge=p, halo=g, dtype="float64", case="tc5")
+        dist.barrier()
+        hist = history.ZarrHistory.open(store)
+        for k in range(2):
+            assert st.write_history(hist, *dev, step=13 + k, time=(13 + k) * dt) == k
+        whole, meta = hist.read(-1)
+        mine = {name: whole[name][st.tiles] for name in "huv"}
+        mnow = st.diagnostics(*dev).cpu().numpy()
+        good = good and len(hist) == 2 and meta["step"] == 14 and abs(meta["mass"] - mnow[0]) <= 1e-15 * mnow[0]
+        good = good and all(np.array_equal(mine[name], x.cpu().numpy()) for name, x in zip("huv", dev))
+        dist.barrier()
+        if rank == 0:
+            import shutil
+            shutil.rmtree(box[0])
     ok = ok and good
     print(f"rank {rank}/{world} C{N} p={p} overlap={overlap} entry_sums={entry} halo={path}: max rel err {max(errs):.2e}, mass drift {(m1[0]-m0[0])/m0[0]:.1e} -> {'ok' if good else 'FAIL'}", flush=True)
     if "peer stores" in st.halo_path and st.ctx.halo_peer_timeouts() != 0:
