@@ -491,6 +491,8 @@ def run_ours(args):
                 "what": "exchange_us = the cross-GPU part of one ghost fill (push + pull, or pack + all-to-all + unpack), alone on an idle GPU, max over ranks; "
                         "exposed = step time minus the time of the same step with the cross-GPU exchange left out",
                 "path": stepper.halo_path}
+        stepper.check_peers()                       # a pull that gave up waiting (stale ghosts) fails the run, loudly
+        halo["peer_wait_timeouts"] = 0
         if "peer stores" in stepper.halo_path and not args.no_secondary and not args.second_order:
             # the comparison arm: the same job with pack -> NCCL all-to-all -> unpack
             alt = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,

@@ -323,8 +323,10 @@ CS_API int cs_halo_peer_connect_pointers(cs_ctx* ctx, int n_peers, int my_rank, 
                                   const int64_t* remote_offsets);
 CS_API int cs_halo_push(cs_ctx* ctx, const void* h, const void* u, const void* v, int nfields, void* stream);
 CS_API int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields, void* stream);
-/* How many times a pull gave up waiting for a peer's flag (about two seconds each; the ghosts of that fill are then stale).
- * Non-zero means the ranks' fills fell out of step or a peer died.  Synchronises with the device. */
+/* How many waits of a pull gave up before a peer's flag arrived (option "peer_timeout_ms", default 5000; the ghosts of
+ * that fill are then stale).  Non-zero means the ranks' fills fell out of step or a peer died; the failure is sticky:
+ * once a wait has given up, no later pull of this context waits, so a broken job drains instead of paying the time-out
+ * on every fill.  Callers check this where they synchronise anyway (the Python mirror raises).  Synchronises. */
 CS_API int cs_halo_peer_timeouts(cs_ctx* ctx, unsigned int* count_host);
 
 /*
@@ -372,7 +374,7 @@ CS_API int cs_diagnostics_noalloc(int dtype, int N, int tiles_per_edge, int halo
 /*
  * Tuning knobs of one context, by name (the CS_* environment variables of DESIGN.md section 4 set the same knobs
  * for every context at creation): "march_prefetch", "march_rows", "march_vec", "march_unit", "reserve_sms",
- * "tma_ring", "fused_halo", "step_graph", "fused_diag", "step_kernel".  Drops the context's captured step graphs.
+ * "tma_ring", "fused_halo", "step_graph", "fused_diag", "step_kernel", "peer_timeout_ms".  Drops the context's captured step graphs.
  * Replaces: nothing (tuning).
  */
 CS_API int cs_ctx_set_option(cs_ctx* ctx, const char* name, int value);

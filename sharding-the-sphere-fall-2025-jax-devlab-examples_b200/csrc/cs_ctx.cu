@@ -39,7 +39,7 @@ extern "C" int cs_ctx_set_option(cs_ctx* ctx, const char* name, int value) {
     struct { const char* key; int* slot; } opts[] = {
         {"march_prefetch", &ctx->tune.march_prefetch}, {"march_rows", &ctx->tune.march_rows}, {"march_vec", &ctx->tune.march_vec},
         {"march_unit", &ctx->tune.march_unit},         {"reserve_sms", &ctx->tune.reserve_sms}, {"tma_ring", &ctx->tune.tma_ring},
-        {"fused_halo", &ctx->tune.fused_halo},         {"step_graph", &ctx->tune.step_graph},   {"fused_diag", &ctx->tune.fused_diag},
+        {"peer_timeout_ms", &ctx->tune.peer_timeout_ms}, {"fused_halo", &ctx->tune.fused_halo},         {"step_graph", &ctx->tune.step_graph},   {"fused_diag", &ctx->tune.fused_diag},
         {"step_kernel", &ctx->tune.step_kernel},
     };
     for (auto& o : opts)
@@ -194,6 +194,10 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
     if (prop.major != 10)
         return bail(cs_fail(ctx, CS_E_CUDA, "device %d is sm_%d%d; this library carries sm_100a code only", ctx->device, prop.major, prop.minor));
     ctx->num_sms = prop.multiProcessorCount;
+    {
+        int khz = 0;                                      // (cudaDeviceProp::clockRate is gone from newer toolkits)
+        if (cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device) == cudaSuccess && khz > 0) ctx->clock_khz = khz;
+    }
 
     int rc;
     if ((rc = build_tables(ctx, cfg->tangents))) return bail(rc);
@@ -239,6 +243,7 @@ extern "C" int cs_ctx_create(const cs_config* cfg, cs_ctx** out) {
     tu.reserve_sms = env_int("CS_MARCH_RESERVE_SMS", tu.reserve_sms);
     tu.tma_ring = env_int("CS_TMA_RING", tu.tma_ring);
     tu.fused_halo = env_int("CS_FUSED_HALO", tu.fused_halo);
+    tu.peer_timeout_ms = env_int("CS_PEER_TIMEOUT_MS", tu.peer_timeout_ms);
     tu.step_graph = env_int("CS_STEP_GRAPH", tu.step_graph);
     tu.fused_diag = env_int("CS_FUSED_DIAG", tu.fused_diag);
     tu.step_kernel = env_int("CS_STEP_KERNEL", tu.step_kernel);

@@ -44,6 +44,7 @@ struct CsTuning {
     int reserve_sms = 12;        // CS_MARCH_RESERVE_SMS: SMs left to the exchange stream by a split stage
     int tma_ring = 6;            // CS_TMA_RING
     int fused_halo = 1;          // CS_FUSED_HALO: 0 vetoes cfg.fused_halo
+    int peer_timeout_ms = 5000;  // CS_PEER_TIMEOUT_MS: how long a one-sided pull waits for a peer's flag before it gives up
     int step_graph = 1;          // CS_STEP_GRAPH: 0 = cs_step enqueues its launches instead of replaying a graph
     int step_debug = 0;          // CS_STEP_DEBUG: timing experiments on the step kernel (wrong results)
     int step_kernel = 0;         // CS_STEP_KERNEL: 1 = cs_step uses the one-launch-per-step kernel where it can (measured
@@ -99,6 +100,7 @@ struct cs_ctx {
     std::vector<double> x_base;                  // the N centre tangents the context was created with
     int4* d_push = nullptr;                      // [T][4] (dst local tile or -1, dst edge, reverse, code)
     bool push_complete = false;                  // every neighbour tile is local
+    int clock_khz = 1500000;                     // SM clock of the device (cudaDevAttrClockRate), for time-outs in cycles
     bool stage_pushed = false;                   // the last stage launch stored the edge ghosts itself
     bool stage_diag_fused = false;               // the last stage launch wrote its diag_out itself (K3 fused into K2)
     bool pdl = false;                            // programmatic dependent launch for stage / halo kernels (CS_PDL=1: on)

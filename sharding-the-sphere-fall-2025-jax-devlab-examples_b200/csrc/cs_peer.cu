@@ -82,21 +82,28 @@ halo_push_kernel(const R* __restrict__ h, const R* __restrict__ u, const R* __re
     }
 }
 
-// Wait (thread 0 of every block) until every source rank's flag for this fill has arrived.
+// Wait (thread 0 of every block) until every source rank's flag for this fill has arrived.  Epochs wrap: compared as a
+// signed difference.  A peer that never issues this fill (a rank that died, or a caller that did not keep the ranks'
+// fills in step) must not hang the GPU: after `timeout` SM cycles the wait gives up and counts the event
+// (cs_halo_peer_timeouts).  The failure is sticky -- once a wait has timed out no later one waits at all, so a broken
+// job drains at full speed instead of paying the timeout on every fill -- and the host mirror raises on it.
 __device__ __forceinline__ void wait_for_peers(const unsigned int* flags, const int64_t* peer_off, int n_peers, int me, int parity,
-                                               unsigned int epoch, unsigned int* counters) {
-    if (threadIdx.x == 0) {
+                                               unsigned int epoch, unsigned int* counters, long long timeout) {
+    if (threadIdx.x == 0 && *(volatile unsigned int*)&counters[4] == 0u) {
         for (int r = 0; r < n_peers; ++r) {
             if (r == me || peer_off[r + 1] == peer_off[r]) continue;
             const unsigned int* f = flags + parity * n_peers + r;
             const long long t_start = clock64();
+            bool gave_up = false;
             while ((int)(ld_acquire_sys(f) - epoch) < 0) {
                 __nanosleep(64);
-                if (clock64() - t_start > 4000000000LL) {
+                if (clock64() - t_start > timeout || *(volatile unsigned int*)&counters[4] != 0u) {
                     atomicAdd(&counters[4], 1u);
+                    gave_up = true;
                     break;
                 }
             }
+            if (gave_up) break;
         }
     }
     __syncthreads();
@@ -115,10 +122,10 @@ __global__ void __launch_bounds__(PEER_THREADS)
 halo_interp_pull_kernel(R* h, R* u, R* v, const int32_t* __restrict__ dst, const int4* __restrict__ src, const R* __restrict__ w,
                         const R* __restrict__ rot, const R* recv0, const R* recv1, const unsigned int* flags,
                         const int64_t* __restrict__ peer_off, int n_peers, int me, int64_t rows, int field_elems, int nfields,
-                        unsigned int* counters) {
+                        unsigned int* counters, long long timeout) {
     const unsigned int epoch = counters[1] + 1u;
     const int parity = (int)(epoch & 1u);
-    wait_for_peers(flags, peer_off, n_peers, me, parity, epoch, counters);
+    wait_for_peers(flags, peer_off, n_peers, me, parity, epoch, counters, timeout);
     const R* recv = parity ? recv1 : recv0;
     auto get = [&](const R* f, int fi, int o) -> R {
         return o < field_elems ? f[o] : __ldcg(recv + (size_t)(o - field_elems) * nfields + fi);
@@ -150,13 +157,11 @@ template <typename R>
 __global__ void __launch_bounds__(PEER_THREADS)
 halo_pull_kernel(R* __restrict__ h, R* __restrict__ u, R* __restrict__ v, const int32_t* __restrict__ dst,
                  const uint8_t* __restrict__ code, const R* recv0, const R* recv1, const unsigned int* flags,
-                 const int64_t* __restrict__ peer_off, int n_peers, int me, int64_t count, int nfields, unsigned int* counters) {
+                 const int64_t* __restrict__ peer_off, int n_peers, int me, int64_t count, int nfields, unsigned int* counters,
+                 long long timeout) {
     const unsigned int epoch = counters[1] + 1u;
     const int parity = (int)(epoch & 1u);
-    // epochs wrap: compared as a signed difference.  A peer that never issues this fill (a rank that died, or a caller
-    // that did not keep the ranks' fills in step) must not hang the GPU: after about two seconds the wait gives up,
-    // counts the event (cs_halo_peer_timeouts) and the scatter goes on with stale data
-    wait_for_peers(flags, peer_off, n_peers, me, parity, epoch, counters);
+    wait_for_peers(flags, peer_off, n_peers, me, parity, epoch, counters, timeout);   // on a time-out the scatter goes on with stale data
     const R* buf = parity ? recv1 : recv0;
     for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < count; k += (int64_t)gridDim.x * blockDim.x) {
         int r = 0;
@@ -333,6 +338,8 @@ extern "C" int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields,
     CS_ON_DEVICE(ctx, ctx->device);
     cudaStream_t s = (cudaStream_t)stream;
     unsigned int* counters = P->flags + 2 * P->n_peers;
+    // option "peer_timeout_ms" (CS_PEER_TIMEOUT_MS; default 5000) in SM cycles at the device's nominal clock
+    const long long timeout = (long long)(ctx->tune.peer_timeout_ms > 0 ? ctx->tune.peer_timeout_ms : 1) * ctx->clock_khz;
     if (ctx->interp_sharded) {
         const int grid = grid_for(ctx, ctx->n_interp);
         if (ctx->dtype == CS_F64)
@@ -340,13 +347,13 @@ extern "C" int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields,
                                                                          (const double*)ctx->d_interp_w, (const double*)ctx->d_interp_rot,
                                                                          (const double*)P->recv[0], (const double*)P->recv[1], P->flags,
                                                                          ctx->d_recv_off, P->n_peers, P->me, ctx->n_interp,
-                                                                         (int)ctx->field_elems, nfields, counters);
+                                                                         (int)ctx->field_elems, nfields, counters, timeout);
         else
             halo_interp_pull_kernel<float><<<grid, PEER_THREADS, 0, s>>>((float*)h, (float*)u, (float*)v, ctx->d_interp_dst, ctx->d_interp_src,
                                                                         (const float*)ctx->d_interp_w, (const float*)ctx->d_interp_rot,
                                                                         (const float*)P->recv[0], (const float*)P->recv[1], P->flags,
                                                                         ctx->d_recv_off, P->n_peers, P->me, ctx->n_interp,
-                                                                        (int)ctx->field_elems, nfields, counters);
+                                                                        (int)ctx->field_elems, nfields, counters, timeout);
         ctx->launches++;
         CS_CUDA(ctx, cudaGetLastError());
         return CS_OK;
@@ -355,11 +362,11 @@ extern "C" int cs_halo_pull(cs_ctx* ctx, void* h, void* u, void* v, int nfields,
     if (ctx->dtype == CS_F64)
         halo_pull_kernel<double><<<grid, PEER_THREADS, 0, s>>>((double*)h, (double*)u, (double*)v, ctx->d_recv_dst, ctx->d_recv_code,
                                                               (const double*)P->recv[0], (const double*)P->recv[1], P->flags, ctx->d_recv_off,
-                                                              P->n_peers, P->me, ctx->recv_total, nfields, counters);
+                                                              P->n_peers, P->me, ctx->recv_total, nfields, counters, timeout);
     else
         halo_pull_kernel<float><<<grid, PEER_THREADS, 0, s>>>((float*)h, (float*)u, (float*)v, ctx->d_recv_dst, ctx->d_recv_code,
                                                              (const float*)P->recv[0], (const float*)P->recv[1], P->flags, ctx->d_recv_off,
-                                                             P->n_peers, P->me, ctx->recv_total, nfields, counters);
+                                                             P->n_peers, P->me, ctx->recv_total, nfields, counters, timeout);
     ctx->launches++;
     CS_CUDA(ctx, cudaGetLastError());
     return CS_OK;

@@ -133,10 +133,25 @@ class ShardedStepper:
     def launches(self):
         return self.ctx.launches + self._extra_launches
 
+    def peer_timeouts(self):
+        """How many one-sided halo waits on this rank gave up (synchronises).  0 in a healthy run."""
+        return self.ctx.halo_peer_timeouts() if getattr(self, "_peer", False) else 0
+
+    def check_peers(self):
+        """Raise if a pull of the one-sided exchange has given up waiting for a peer (option ``peer_timeout_ms``, default
+        5 s): from that fill on the ghosts are stale and no later pull waits, so the results are not to be used."""
+        n = self.peer_timeouts()
+        if n:
+            raise RuntimeError(f"rank {self.rank}: {n} one-sided halo wait(s) timed out -- a peer did not issue its ghost "
+                               "fill (ranks out of step, or a rank died); results since then are invalid")
+
     def close(self):
         # graphs hold NCCL work: drop them (and drain the device) before the process group goes away
         self._graphs.clear()
         torch.cuda.synchronize(self.device)
+        if self.peer_timeouts():
+            import warnings
+            warnings.warn(f"rank {self.rank}: one-sided halo waits timed out during this run (see check_peers)")
         if self.world > 1 and getattr(self, "_peer", False) and dist.is_initialized():
             dist.barrier(group=self.group)                 # peers hold mappings of this context's buffers
         self.ctx.close()
@@ -347,6 +362,7 @@ class ShardedStepper:
         """:meth:`read_sums_async`, then the rows that were recorded, as a ``[steps, 2]`` tensor (synchronises)."""
         sums, count = self.read_sums_async()
         n = int(count.item())
+        self.check_peers()
         if n > self.history_capacity:
             raise RuntimeError(f"{n} steps recorded, the history holds {self.history_capacity}: read it more often")
         return sums[:n]

@@ -675,3 +675,44 @@ def test_one_sided_exchange_emulated_on_one_gpu(built_library, p, world, tile_ma
     for c in ctxs:
         c.close()
     whole.close()
+
+
+def test_one_sided_pull_gives_up_and_says_so(built_library):
+    """A pull whose peer never pushes must not hang the GPU: it gives up after `peer_timeout_ms`, counts the event,
+    and from then on no pull waits at all (the job drains instead of paying the time-out on every fill)."""
+    import time
+    N, g, p, world = 24, 2, 1, 2
+    from cubesphere import partition
+    ranges = partition.block_ranges(6, world)
+    ctxs, recv_counts = [], []
+    for b, c in ranges:
+        ctx = api.Context(N, tiles_per_edge=p, halo=g, tile_begin=b, tile_count=c)
+        _, recv = ctx.halo_plan([x for x, _ in ranges], [x for _, x in ranges])
+        recv_counts.append(recv)
+        ctx.set_option("peer_timeout_ms", 200)
+        ctxs.append(ctx)
+    _connect_in_process(ctxs, recv_counts)
+    m = N + 2 * g
+    sh = [[torch.zeros((c, m, m), dtype=torch.float64, device="cuda") for _ in range(3)] for _, c in ranges]
+    assert ctxs[0].halo_peer_timeouts() == 0
+    ctxs[0].halo_push(*sh[0])                    # rank 0 does its part, rank 1 never pushes
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    ctxs[0].halo_pull(*sh[0])
+    torch.cuda.synchronize()
+    waited = time.perf_counter() - t0
+    assert 0.1 < waited < 2.0, waited            # about the 200 ms asked for, not the default and not for ever
+    assert ctxs[0].halo_peer_timeouts() >= 1
+    t0 = time.perf_counter()
+    for _ in range(5):                           # sticky: later pulls do not wait
+        ctxs[0].halo_push(*sh[0])
+        ctxs[0].halo_pull(*sh[0])
+    torch.cuda.synchronize()
+    assert time.perf_counter() - t0 < 0.1
+    # the healthy direction still works: rank 1 has rank 0's pushes
+    ctxs[1].halo_push(*sh[1])
+    ctxs[1].halo_pull(*sh[1])
+    torch.cuda.synchronize()
+    assert ctxs[1].halo_peer_timeouts() == 0
+    for c in ctxs:
+        c.close()

@@ -6,13 +6,14 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT / "sharding-the-sphere-fall-2025-jax-devlab-examples_b200"))
+import os  # noqa: E402
 import torch  # noqa: E402
 from cubesphere import api  # noqa: E402
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 1536
 dtype = sys.argv[2] if len(sys.argv) > 2 else "f32"
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
-ctx = api.Context(N, halo=2, dtype=dtype, sums_of_entry_state=True)
+ctx = api.Context(N, halo=2, dtype=dtype, sums_of_entry_state=True, fused_halo=bool(os.environ.get("PROF_FUSED_HALO")))
 gen = torch.Generator(device="cuda").manual_seed(1)
 h = 1000.0 + 10.0 * torch.rand(ctx.shape, device="cuda", dtype=ctx.dtype, generator=gen)
 u = 1e-6 * torch.rand(ctx.shape, device="cuda", dtype=ctx.dtype, generator=gen)
