@@ -298,3 +298,15 @@ def test_interp_exchange_plan_serial_emulation(N, p, world, tile_map):
                 d = np.isin(np.arange(wt.size), plans[r].dst) & np.isin((np.arange(wt.size) + b * m * m) if tile_map == "block" else np.full(wt.size, -1), halo.dst)
                 if tile_map == "block":
                     assert np.abs(got.reshape(-1)[d] - wt[d]).max() <= 1e-13
+
+
+def test_integration_notes_name_every_entry_point():
+    """INTEGRATION.md is the maintainer's map of the ABI: an entry point added to the header without a word there fails."""
+    import re
+    root = Path(__file__).resolve().parent.parent
+    header = (root / "include" / "cubesphere.h").read_text()
+    notes = (root / "INTEGRATION.md").read_text()
+    names = set(re.findall(r"CS_API\s+[\w\s\*]+?\b(cs_\w+)\s*\(", header))
+    assert len(names) > 30
+    missing = sorted(n for n in names if n not in notes)
+    assert not missing, missing
