@@ -558,6 +558,7 @@ def run_ours(args):
                                "value": cells_total / (ms_single * 1e-3), "ms_per_step": ms_single}}
     else:
         e2e = stepper.time_e2e(pinned, dev, dt, max(3, min(args.steps, 5)), cells_total)
+        stepper.check_peers()                       # ... and none of the end-to-end fills ran on stale ghosts either
 
     clk.stop()
 
