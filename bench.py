@@ -419,6 +419,18 @@ def run_ours(args):
         one_step(False)
     ms_nosums, _ = timed_steps(args.steps, with_sums=False)
 
+    def peer_wait_timeouts():
+        """One-sided exchange only: pulls (summed over the ranks) that gave up waiting for a peer so far.  Non-zero means
+        ghosts went stale at some fill and every number measured after it is void."""
+        if world == 1:
+            return 0
+        t = torch.tensor([stepper.peer_timeouts()], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t)
+        return int(t.item())
+
+    if peer_wait_timeouts():                       # the same count on every rank: all of them stop here
+        raise RuntimeError("a one-sided halo wait timed out during the timed steps: the headline number is void")
+
     # ---- roofline of the dominant kernel (fused RK stage), timed per launch inside a CUDA graph --------------
     peak, peak_kind = measured_peak_gbs()
     roof = stepper.time_stage_kernel(dev, dt, reps=10)
@@ -491,8 +503,7 @@ def run_ours(args):
                 "what": "exchange_us = the cross-GPU part of one ghost fill (push + pull, or pack + all-to-all + unpack), alone on an idle GPU, max over ranks; "
                         "exposed = step time minus the time of the same step with the cross-GPU exchange left out",
                 "path": stepper.halo_path}
-        stepper.check_peers()                       # a pull that gave up waiting (stale ghosts) fails the run, loudly
-        halo["peer_wait_timeouts"] = 0
+        halo["peer_wait_timeouts"] = peer_wait_timeouts()      # 0 in a healthy run; otherwise this leg's numbers are void
         if "peer stores" in stepper.halo_path and not args.no_secondary and not args.second_order:
             # the comparison arm: the same job with pack -> NCCL all-to-all -> unpack
             alt = sharded.ShardedStepper(N, tiles_per_edge=p, halo=g, dtype=args.dtype, axis=case.axis,
@@ -558,7 +569,9 @@ def run_ours(args):
                                "value": cells_total / (ms_single * 1e-3), "ms_per_step": ms_single}}
     else:
         e2e = stepper.time_e2e(pinned, dev, dt, max(3, min(args.steps, 5)), cells_total)
-        stepper.check_peers()                       # ... and none of the end-to-end fills ran on stale ghosts either
+        e2e["peer_wait_timeouts"] = peer_wait_timeouts()       # ... and so are these, if any end-to-end fill gave up
+        if e2e["peer_wait_timeouts"]:
+            e2e["value"] = None
 
     clk.stop()
 
