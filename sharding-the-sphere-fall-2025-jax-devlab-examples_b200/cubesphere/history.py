@@ -13,6 +13,8 @@ Layout of a history::
     <path>/h, u, v      [record, tile, y, x]     chunks [1, 1, m, m]: ONE FILE PER (record, tile)
     <path>/time, mass, energy   [record] f8      chunks [256]
     <path>/step                 [record] i8      chunks [256]
+    <path>/lon, lat     [tile, y, x] f8          degrees at the cell centres (ghost cells: the tile's own chart extended),
+                                                 written once at creation; the fields name them as CF "coordinates"
 
 One chunk per (record, tile) is what makes the store fit the sharded solver: a rank writes the chunk files of the tiles
 it owns, straight from its own shard -- no gather -- and one rank (``write_meta=True``) appends the scalars and, last of
@@ -45,6 +47,26 @@ def _write_json(path: Path, obj):
     os.replace(tmp, path)               # atomic on POSIX: a reader sees the old or the new file, never half of one
 
 
+def tile_lonlat(N, p, g):
+    """Longitude / latitude in degrees of every cell of the padded tile layout: two arrays [6 p^2, m, m]."""
+    from . import geometry as geo
+    n = N // p
+    frames = np.asarray(geo.FACE_FRAMES, dtype=np.float64)
+    lon = np.empty((6 * p * p, n + 2 * g, n + 2 * g))
+    lat = np.empty_like(lon)
+    ext = np.tan(-0.25 * np.pi + (np.arange(-g, N + g) + 0.5) * (0.5 * np.pi / N))     # the chart continued past the edges
+    ext[g:g + N] = geo.centre_tangents(N)                                              # interior: the solver's own table
+    for t in range(6 * p * p):
+        f, r = divmod(t, p * p)
+        ty, tx = divmod(r, p)
+        X, Y = np.meshgrid(ext[tx * n:tx * n + n + 2 * g], ext[ty * n:ty * n + n + 2 * g], indexing="xy")
+        P = frames[f, 0] + X[..., None] * frames[f, 1] + Y[..., None] * frames[f, 2]
+        P /= np.linalg.norm(P, axis=-1, keepdims=True)
+        lo, la = geo.lonlat(P)
+        lon[t], lat[t] = np.degrees(lo), np.degrees(la)
+    return lon, lat
+
+
 def _zarray(shape, chunks, dtype):
     return {"zarr_format": 2, "shape": [int(x) for x in shape], "chunks": [int(x) for x in chunks], "dtype": dtype,
             "compressor": None, "fill_value": 0 if dtype[1] == "i" else 0.0, "filters": None, "order": "C"}
@@ -63,7 +85,7 @@ class ZarrHistory:
 
     # ---- creation / opening -----------------------------------------------------------------------------------
     @classmethod
-    def create(cls, path, *, N, tiles_per_edge=1, halo=2, dtype="float64", case=None, extra=None):
+    def create(cls, path, *, N, tiles_per_edge=1, halo=2, dtype="float64", case=None, extra=None, coordinates=True):
         path = Path(path)
         if (path / ".zgroup").exists():
             raise FileExistsError(f"{path} already holds a zarr group")
@@ -81,13 +103,22 @@ class ZarrHistory:
         _write_json(path / ".zattrs", attrs)
         for name in FIELDS:
             (path / name).mkdir(exist_ok=True)
-            _write_json(path / name / ".zattrs", {"_ARRAY_DIMENSIONS": ["record", "tile", "y", "x"]})
+            _write_json(path / name / ".zattrs", dict({"_ARRAY_DIMENSIONS": ["record", "tile", "y", "x"]},
+                                                      **({"coordinates": "lon lat"} if coordinates else {})))
             _write_json(path / name / ".zarray", _zarray((0, self.tiles, self.m, self.m), (1, 1, self.m, self.m),
                                                           dt.newbyteorder("<").str))
         for name, code in SCALARS:
             (path / name).mkdir(exist_ok=True)
             _write_json(path / name / ".zattrs", {"_ARRAY_DIMENSIONS": ["record"]})
             _write_json(path / name / ".zarray", _zarray((0,), (SCALAR_CHUNK,), code))
+        if coordinates:
+            for name, a, long_name in zip(("lon", "lat"), tile_lonlat(N, tiles_per_edge, halo), ("longitude", "latitude")):
+                (path / name).mkdir(exist_ok=True)
+                _write_json(path / name / ".zattrs", {"_ARRAY_DIMENSIONS": ["tile", "y", "x"], "units": "degrees_" +
+                                                      ("east" if name == "lon" else "north"), "long_name": long_name})
+                for t in range(self.tiles):
+                    a[t].astype("<f8").tofile(path / name / f"{t}.0.0")
+                _write_json(path / name / ".zarray", _zarray(a.shape, (1, self.m, self.m), "<f8"))
         return self
 
     @classmethod

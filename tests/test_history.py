@@ -103,3 +103,31 @@ def test_scalar_chunks_and_errors(tmp_path, monkeypatch):
         history.ZarrHistory.open(tmp_path / "nothing")
     with pytest.raises(ValueError):
         history.ZarrHistory.create(tmp_path / "x", N=5, tiles_per_edge=2)
+
+
+def test_coordinates_are_written_once(tmp_path):
+    """lon / lat of every stored cell (CF 'coordinates' of the fields): interior cells are where the initial conditions
+    were sampled, and a ghost cell's coordinates are those of the neighbour cell it mirrors only to first order (the
+    tile's own chart extended), which is what a plot of the padded arrays wants."""
+    from cubesphere import geometry as geo
+    N, p, g = 8, 2, 2
+    history.ZarrHistory.create(tmp_path / "h", N=N, tiles_per_edge=p, halo=g)
+    root = tmp_path / "h"
+    lon, lat = zarr_v2_read(root / "lon"), zarr_v2_read(root / "lat")
+    assert lon.shape == lat.shape == (24, 8, 8)
+    assert json.loads((root / "h" / ".zattrs").read_text())["coordinates"] == "lon lat"
+    patch = geo.Patch(N, p)
+    lo, la = geo.lonlat(patch.points())
+    assert np.allclose(lon[:, g:-g, g:-g], np.degrees(lo), atol=1e-12)
+    assert np.allclose(lat[:, g:-g, g:-g], np.degrees(la), atol=1e-12)
+    assert np.all((lon >= 0) & (lon < 360)) and np.all(np.abs(lat) <= 90)
+    # ghosts continue the tile's own chart: across an inner tile edge they ARE the neighbour tile's interior cells
+    assert np.allclose(lat[0][g:-g, -g:], lat[1][g:-g, g:2 * g], atol=1e-12)
+    # ... and across a cube edge they lie beyond it: one cell further along the same coordinate line, not wrapped around
+    east = lon[1][g:-g, -g - 1:]                                    # last interior column and the two ghosts of tile 1
+    step = np.diff(np.unwrap(np.radians(east), axis=1), axis=1)
+    assert np.all(step[:, 0] * step[:, 1] > 0) and np.all(np.abs(step) < np.radians(360.0 / (4 * N) * 2))
+    # face 4 / 5 hold the poles (whichever the frames put there): some tile reaches |lat| > 80
+    assert np.abs(lat).max() > 80
+    history.ZarrHistory.create(tmp_path / "bare", N=N, coordinates=False)
+    assert not (tmp_path / "bare" / "lon").exists()
