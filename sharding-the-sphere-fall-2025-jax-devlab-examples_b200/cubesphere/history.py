@@ -207,3 +207,19 @@ class ZarrHistory:
         meta = dict(self.attrs, record=k, step=int(sc["step"][k]), time=float(sc["time"][k]), mass=float(sc["mass"][k]),
                     energy=float(sc["energy"][k]))
         return state, meta
+
+
+def write_sharded(hist, state, *, tile_ids, rank, barrier, step, time, mass=float("nan"), energy=float("nan")):
+    """One record written by all ranks of a job (every rank has opened the same store on a shared file system and calls
+    this with its own shard): each rank writes the chunk files of the tiles it owns, rank 0 adds the scalars and
+    publishes the record once everybody is done.  ``barrier`` is the job's barrier (``torch.distributed.barrier``, or a
+    no-op for one rank).  Returns the record index."""
+    record = len(hist)                      # the same on every rank: nothing of this record is published yet ...
+    barrier()                               # ... and nobody publishes before everybody has read it
+    if rank != 0:
+        hist.append(state, step=step, time=time, tile_ids=tile_ids, write_meta=False, record=record)
+    barrier()
+    if rank == 0:
+        hist.append(state, step=step, time=time, mass=mass, energy=energy, tile_ids=tile_ids, record=record)
+    barrier()
+    return record

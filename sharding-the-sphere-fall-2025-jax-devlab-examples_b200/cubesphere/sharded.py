@@ -379,20 +379,11 @@ class ShardedStepper:
         shared file system).  Each rank writes the chunk files of the tiles it owns straight from its shard -- the
         fields are never gathered; rank 0 adds the scalars (with the whole-sphere mass / energy) and publishes the record
         after a barrier.  Synchronises; not for the timed path."""
+        from . import history
         sums = self.diagnostics(h, u, v).cpu().numpy()
-        record = len(hist)                                      # the same on every rank: nothing is published yet
-        if self.world > 1:
-            dist.barrier(group=self.group)                      # ... and nobody publishes before everybody has read it
-        ids = self.tiles
-        if self.rank != 0:
-            hist.append({"h": h, "u": u, "v": v}, step=step, time=time, tile_ids=ids, write_meta=False, record=record)
-        if self.world > 1:
-            dist.barrier(group=self.group)
-        if self.rank == 0:
-            hist.append({"h": h, "u": u, "v": v}, step=step, time=time, mass=sums[0], energy=sums[1], tile_ids=ids, record=record)
-        if self.world > 1:
-            dist.barrier(group=self.group)
-        return record
+        barrier = (lambda: dist.barrier(group=self.group)) if self.world > 1 else (lambda: None)
+        return history.write_sharded(hist, {"h": h, "u": u, "v": v}, tile_ids=self.tiles, rank=self.rank, barrier=barrier,
+                                     step=step, time=time, mass=sums[0], energy=sums[1])
 
     # -- measurement helpers used by bench.py ---------------------------------------------------
     def time_stage_kernel(self, state, dt, reps=10, rounds=3):

@@ -177,6 +177,21 @@ for r in reqs: r.wait()
 plan.fill_local(shard)
 plan.unpack([x.numpy() for x in recv], shard)
 ok = all(np.array_equal(a, w[b:b + c]) for a, w in zip(shard, ref))
+# the history store, written by both ranks: each its own tiles' chunks, rank 0 publishes (two records)
+from pathlib import Path
+from cubesphere import history
+store = Path(sys.argv[3]) / "run.zarr"
+if rank == 0:
+    history.ZarrHistory.create(store, N=N, tiles_per_edge=p, halo=g)
+dist.barrier()
+hist = history.ZarrHistory.open(store)
+state = dict(zip("huv", shard))
+for k in range(2):
+    rec = history.write_sharded(hist, {n: x + k for n, x in state.items()}, tile_ids=range(b, b + c), rank=rank,
+                                barrier=dist.barrier, step=5 * k, time=0.5 * k, mass=1.0, energy=2.0)
+    ok = ok and rec == k
+whole, meta = hist.read(-1)
+ok = ok and len(hist) == 2 and meta["step"] == 5 and all(np.array_equal(whole[n], w + 1) for n, w in zip("huv", ref))
 t = torch.tensor([int(ok)]); dist.all_reduce(t, op=dist.ReduceOp.MIN)
 dist.destroy_process_group()
 sys.exit(0 if int(t.item()) == 1 else 1)
@@ -189,7 +204,7 @@ def test_exchange_over_gloo_world2(tmp_path):
     pkg = ROOT / "sharding-the-sphere-fall-2025-jax-devlab-examples_b200"
     env = dict(os.environ, OMP_NUM_THREADS="1")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-           "--master-addr", "127.0.0.1", "--master-port", "29731", str(script), str(pkg), str(ROOT)]
+           "--master-addr", "127.0.0.1", "--master-port", "29731", str(script), str(pkg), str(ROOT), str(tmp_path)]
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
 
